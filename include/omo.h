@@ -1,0 +1,172 @@
+/*
+ * omo.h -- C ABI of the B200 objective engine (libomo.so, built from optimo_b200/csrc/).
+ *
+ * This is the drop-in boundary for OptiMo's objective(+gradient) hot path. Every entry point takes plain
+ * pointers and sizes; no C++ / torch types cross it. All paths below are relative to the reference checkout.
+ *
+ *   What it replaces                                             Reference
+ *   ------------------------------------------------------------ ------------------------------------------
+ *   Core::CalculateFullObjective (f = C + D_param + D_traj)      OptiMo/core_rbdl.cpp:348-401
+ *   Core::SetStates (time grid, curve / IK / FK sampling,        OptiMo/core_rbdl.cpp:108-166, :28-95
+ *       4th-order stencils)
+ *   Core::CalculateCost (RNEA loop, time-varying weight)         OptiMo/core_rbdl.cpp:307-346
+ *   RBDL InverseDynamics / jcalc / InverseKinematics             external/rbdl-v2.5.0/src/Dynamics.cc:26-105,
+ *                                                                src/Joint.cc:21-210, src/Kinematics.cc:615-709
+ *   Curve::GetValue (segment lookup, Newton, Bernstein)          OptiMo/curve.cpp:43-93,100-128
+ *   Object::SetDescriptor / MakeMotionCyclic                     OptiMo/object.cpp:147-186, curve.cpp:179-188
+ *   Core::InitializeDynamicsModel (body table)                   OptiMo/core_rbdl.cpp:200-262
+ *   Core::OptimizationCache (per-sample q, qd, qdd, tau, cost)   OptiMo/core.h:120-152, core_rbdl.cpp:341-343
+ *
+ * plus one NEW output the reference does not have: a central finite-difference gradient
+ * on the free parameters, evaluated as one batch of 2F+1 objective columns.
+ *
+ * Conventions
+ *   - every function returns an omo_status; omo_last_error(ctx) gives the message of the last failure.
+ *   - the caller owns every host buffer it passes; an omo_ctx owns all device memory, streams and staging.
+ *   - one omo_ctx is bound to one CUDA device and may be used by one host thread at a time.
+ *   - there is NO CPU fallback: without a usable CUDA device omo_create fails with OMO_CUDA_ERROR.
+ *   - all arithmetic is IEEE binary64.
+ */
+#ifndef OMO_H
+#define OMO_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum omo_status {
+    OMO_OK = 0,
+    OMO_BAD_ARG = 1,     /* null pointer, size mismatch, unsupported scene (too many joints, ...) */
+    OMO_CUDA_ERROR = 2,  /* any CUDA runtime failure, including "no device" */
+    OMO_NCCL_ERROR = 3,
+    OMO_OOM = 4,
+    OMO_NOT_READY = 5    /* window / weights / original parameters not set yet */
+} omo_status;
+
+typedef struct omo_ctx omo_ctx;
+
+/* Limits of the sm_100a kernels (scene tables live in constant memory). */
+#define OMO_MAX_JOINTS 128
+#define OMO_MAX_IK 8
+#define OMO_MAX_IK_CHAIN 8 /* rotating joints per IK chain (end effector excluded) */
+
+/*
+ * Flattened scene == what Core::ReadJson + Core::InitializeDynamicsModel leave behind
+ * (OptiMo/core_io.cpp:228-250, core_rbdl.cpp:200-262).
+ *
+ * Joints are listed in Object::GetJoints() order (DFS pre-order, OptiMo/object.cpp:27-40), which is also
+ * RBDL body id - 1 and q_index / 3. parent[0] == -1 is the root.
+ *
+ * Channels are the keyframable variables in Object::GetItems() order (object.cpp:47-61): channel 3*j+a is
+ * rot_{x,y,z}[a] of joint j; channel 3*J + 3*h + a is pos_{x,y,z}[a] of IK handler h. The descriptor
+ * x in R^{5*n_cp} lists, channel by channel, the control points of every KEYED channel in insertion order,
+ * 5 doubles each: (time, value, theta, time_backward, time_forward) (object.cpp:110-145, curve.h:39-54).
+ */
+typedef struct omo_scene_desc {
+    int n_joints;              /* J, root included */
+    const int* parent;         /* [J] */
+    const double* offset;      /* [J*3] Joint::offset_ */
+    const double* mass;        /* [J]   Joint::mass_ (joint.cpp:90-119); root: 0 */
+    const double* com;         /* [J*3] centre of mass in the joint frame */
+    const double* inertia;     /* [J*9] row-major inertia about the COM */
+    int n_ik;                  /* IK handlers */
+    const int* ik_root;        /* [n_ik] joint index of the chain root (ikhandler.cpp:77-101) */
+    const int* ik_end;         /* [n_ik] joint index of the end effector */
+    int n_channels;            /* 3*J + 3*n_ik */
+    const double* chan_const;  /* [n_channels] Variable::var_ (value of an un-keyed channel) */
+    const int* chan_first_cp;  /* [n_channels] index of the channel's first control point in the descriptor, -1 if un-keyed */
+    const int* chan_n_cp;      /* [n_channels] number of control points (0 if un-keyed) */
+    int n_cp;                  /* total control points; descriptor length D = 5*n_cp */
+    const int* chain;          /* [n_cp] for each keyed channel, at [first_cp, first_cp+n), the channel's control
+                                  points (descriptor-global indices) in segment-list order, i.e. sorted by the
+                                  time they had when they were inserted (curve.cpp:130-148) */
+} omo_scene_desc;
+
+typedef struct omo_gauss { double amp, mu, sigma; } omo_gauss; /* GaussianKernel, OptiMo/core.h:27-33 */
+
+/* Per-candidate breakdown of f (core_rbdl.cpp:381-400). */
+typedef struct omo_terms { double C, D_param, D_traj; } omo_terms;
+
+/* ---- life cycle ------------------------------------------------------------------------------------ */
+omo_status omo_create(const omo_scene_desc* scene, int device, omo_ctx** out);
+void omo_destroy(omo_ctx* ctx);
+const char* omo_last_error(const omo_ctx* ctx); /* ctx may be NULL: error of the last failed omo_create */
+const char* omo_version(void);
+
+/* ---- state the objective reads (snapshotted on the device) ----------------------------------------- */
+/* Time grid: replays `for (t = min_t; t <= max_t; t += dt)` (core_rbdl.cpp:120-123). Needs >= 3 samples. */
+omo_status omo_set_window(omo_ctx* ctx, double min_t, double max_t, double dt);
+/* w_param: Core::CalculateParameterWeights() (core.cpp:161-182), length D. kernels: Core::kernels_ (time-varying
+ * weight, core.cpp:191-199). cyclic: Object::is_cyclic_. */
+omo_status omo_set_weights(omo_ctx* ctx, const double* w_param, int D, double w_traj, const omo_gauss* kernels,
+                           int n_kernels, int cyclic);
+/* x_original (core.h:237-243): uploads it and rebuilds p_original (N_s x 3J) on the device. */
+omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D);
+
+/* ---- queries ---------------------------------------------------------------------------------------- */
+int omo_num_samples(const omo_ctx* ctx);  /* N_s */
+int omo_descriptor_size(const omo_ctx* ctx); /* D */
+int omo_dof(const omo_ctx* ctx);          /* 3*J */
+omo_status omo_get_time_grid(const omo_ctx* ctx, double* t_out /* [N_s] */);
+omo_status omo_get_cost_weights(const omo_ctx* ctx, double* w_out /* [N_s] */);
+omo_status omo_get_p_original(omo_ctx* ctx, double* p_out /* [N_s * 3J], sample-major */);
+
+/* ---- the hot path ----------------------------------------------------------------------------------- */
+/* B candidates, X row-major [B][D] in HOST memory. f_out[B]; terms_out[B] optional (NULL). */
+omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_terms* terms_out);
+
+/* Same with X, f_out (and optional terms_out, 3 doubles per candidate) already in DEVICE memory of ctx's
+ * device. Asynchronous on the ctx stream unless `sync` != 0. */
+omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync);
+
+/* One evaluation that also fills the OptimizationCache of the reference (core.h:120-152): each of
+ * q, qd, qdd, tau is [N_s * dof] sample-major, local_cost is [N_s]; any of them may be NULL. */
+omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd,
+                           double* qdd, double* tau, double* local_cost);
+
+/* Joint world positions p (N_s x 3J, sample-major) of descriptor x (SetStates' p output, core_rbdl.cpp:150-153). */
+omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out);
+
+/* NEW (no reference counterpart): central-difference gradient on the free parameters,
+ *   g_k = (f(x + h e_idx[k]) - f(x - h e_idx[k])) / (2h),
+ * evaluated as ONE batch of 2F+1 columns built on the device from x. f0_out, fpm_out ([F][2] = f+, f-) optional. */
+omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, double* f0_out,
+                         double* grad_out, double* fpm_out);
+
+/* Column-sharded form for multi-GPU: evaluates columns [col_begin, col_begin+col_count) of the (2F+1)-column
+ * perturbation list (column 0 = x, column 2k+1 = x + h e_k, column 2k+2 = x - h e_k) and leaves the values in
+ * DEVICE memory d_f_cols[col_count] (gather them with NCCL, then call omo_grad_from_columns). */
+omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin,
+                                 int col_count, double* d_f_cols, int sync);
+/* grad_k = (cols[2k+1] - cols[2k+2]) / (2h) on the host, from the gathered 2F+1 column values. */
+omo_status omo_grad_from_columns(const double* f_cols, int F, double h, double* f0_out, double* grad_out);
+
+/* Contiguous shard [begin, begin+count) of n items for `rank` of `world` (first ranks take the remainder). */
+void omo_shard_range(int n, int rank, int world, int* begin, int* count);
+
+/* ---- device helpers for harnesses (no reference counterpart) ---------------------------------------- */
+omo_status omo_device_alloc(omo_ctx* ctx, unsigned long long bytes, void** out);
+omo_status omo_device_free(omo_ctx* ctx, void* p);
+omo_status omo_host_alloc_pinned(omo_ctx* ctx, unsigned long long bytes, void** out);
+omo_status omo_host_free_pinned(omo_ctx* ctx, void* p);
+omo_status omo_memcpy_h2d(omo_ctx* ctx, void* dst, const void* src, unsigned long long bytes);
+omo_status omo_memcpy_d2h(omo_ctx* ctx, void* dst, const void* src, unsigned long long bytes);
+omo_status omo_synchronize(omo_ctx* ctx);
+void* omo_stream(omo_ctx* ctx); /* cudaStream_t the hot path launches on */
+
+/* Counters of the last batch (summed over its sample-evals): out[0] Bezier evaluations, out[1] Newton
+ * iterations, out[2] IK solves, out[3] IK iterations, out[4] kernels launched since omo_create. Counting is
+ * done only when `enable` was set by omo_set_counting(ctx, 1) (it costs a few atomics per block). */
+omo_status omo_set_counting(omo_ctx* ctx, int enable);
+omo_status omo_get_counters(omo_ctx* ctx, unsigned long long* out5);
+
+/* Timing of the main objective kernel: accumulates CUDA-event time of every launch between reset and read. */
+omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* launches);
+
+/* Sustained dependent-free DFMA throughput of the device in FLOP/s (roofline denominator; runs ~ms). */
+omo_status omo_measure_dfma_peak(omo_ctx* ctx, double* flops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OMO_H */

@@ -1,0 +1,511 @@
+"""ctypes view of the headless Core (include/optimo_core.h) and of the raw engine ABI (include/omo.h).
+
+Method names follow the reference's `Core` (OptiMo/core.h) so that tests read like calls into the reference.
+Nothing here computes: every number comes out of liboptimo_core.so / libomo.so (CUDA). If the libraries are
+missing, import fails loudly -- there is no CPU path.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_CORE_SO = os.path.join(_HERE, "host", "liboptimo_core.so")
+_OMO_SO = os.path.join(_HERE, "csrc", "libomo.so")
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_vp = C.c_void_p
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+class ForcedStop(RuntimeError):
+    """Mirror of nlopt::forced_stop thrown by EvaluateObjective (core_opt.cpp:50-54)."""
+
+
+def lib_paths():
+    return {"core": _CORE_SO, "omo": _OMO_SO}
+
+
+def _load():
+    for p in (_OMO_SO, _CORE_SO):
+        if not os.path.exists(p):
+            raise ImportError(f"{p} is missing: run `make -C optimo_b200` (or __graft_entry__.build()); there is no fallback path")
+    omo = C.CDLL(_OMO_SO, mode=C.RTLD_GLOBAL)
+    core = C.CDLL(_CORE_SO)
+    return omo, core
+
+
+_omo, _core = _load()
+
+
+def _sig(lib, name, res, args):
+    fn = getattr(lib, name)
+    fn.restype = res
+    fn.argtypes = args
+    return fn
+
+
+ci, cd, cs = C.c_int, C.c_double, C.c_char_p
+_CORE_SIG = {
+    "optimo_last_error": (cs, []),
+    "optimo_core_new": (_vp, []),
+    "optimo_core_instance": (_vp, []),
+    "optimo_core_free": (None, [_vp]),
+    "optimo_read_json": (ci, [_vp, cs]),
+    "optimo_read_json_string": (ci, [_vp, cs]),
+    "optimo_write_json": (ci, [_vp, cs]),
+    "optimo_scene_json": (ci, [_vp, C.c_char_p, ci]),
+    "optimo_set_device": (ci, [_vp, ci]),
+    "optimo_min_frame": (ci, [_vp]),
+    "optimo_max_frame": (ci, [_vp]),
+    "optimo_set_frames": (None, [_vp, ci, ci]),
+    "optimo_num_joints": (ci, [_vp]),
+    "optimo_num_items": (ci, [_vp]),
+    "optimo_item_name": (ci, [_vp, ci, C.c_char_p, ci]),
+    "optimo_descriptor_size": (ci, [_vp]),
+    "optimo_get_descriptor": (ci, [_vp, _dp]),
+    "optimo_set_descriptor": (ci, [_vp, _dp, ci]),
+    "optimo_set_cyclic": (None, [_vp, ci]),
+    "optimo_update_original_parameters": (ci, [_vp, _dp, ci]),
+    "optimo_retrieve_original_parameters": (ci, [_vp, _dp]),
+    "optimo_update_global_weight": (None, [_vp, cd]),
+    "optimo_update_per_item_weight": (ci, [_vp, cd, cs]),
+    "optimo_clear_kernels": (None, [_vp]),
+    "optimo_add_kernel": (None, [_vp, cd, cd, cd]),
+    "optimo_get_cost_weight": (cd, [_vp, cd]),
+    "optimo_parameter_weights": (ci, [_vp, _dp]),
+    "optimo_set_selected": (ci, [_vp, cs, ci]),
+    "optimo_update_freezed_dofs_from_selection": (None, [_vp]),
+    "optimo_get_freezed_dofs": (ci, [_vp, _ip]),
+    "optimo_set_freezed_dofs": (ci, [_vp, _ip, ci]),
+    "optimo_joint_physical": (ci, [_vp, ci, _dp]),
+    "optimo_calculate_full_objective": (ci, [_vp, cd, cd, _dp, _dp, ci, _dp, _dp]),
+    "optimo_calculate_full_objective_batch": (ci, [_vp, cd, cd, _dp, ci, _dp, ci, _dp, _dp]),
+    "optimo_calculate_gradient": (ci, [_vp, cd, cd, _dp, _dp, ci, _ip, ci, cd, _dp, _dp, _dp]),
+    "optimo_positions": (ci, [_vp, cd, cd, _dp, ci, _dp]),
+    "optimo_num_samples": (ci, [_vp, cd, cd]),
+    "optimo_evaluate_objective": (ci, [_vp, _dp, ci, _dp, ci, cd, cd, ci, cd, _dp, _dp]),
+    "optimo_set_stop_optimization": (None, [_vp, ci]),
+    "optimo_get_stop_optimization": (ci, [_vp]),
+    "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
+    "optimo_cache_size": (ci, [_vp, _ip, _ip]),
+    "optimo_get_cache": (ci, [_vp, ci, _dp]),
+    "optimo_clear_optimization_cache": (None, [_vp]),
+    "optimo_engine": (_vp, [_vp]),
+    "optimo_engine_synced": (_vp, [_vp, cd, cd]),
+}
+for _n, (_r, _a) in _CORE_SIG.items():
+    _sig(_core, _n, _r, _a)
+
+_ull = C.c_ulonglong
+_OMO_SIG = {
+    "omo_last_error": (cs, [_vp]),
+    "omo_version": (cs, []),
+    "omo_num_samples": (ci, [_vp]),
+    "omo_descriptor_size": (ci, [_vp]),
+    "omo_dof": (ci, [_vp]),
+    "omo_get_time_grid": (ci, [_vp, _dp]),
+    "omo_get_cost_weights": (ci, [_vp, _dp]),
+    "omo_get_p_original": (ci, [_vp, _dp]),
+    "omo_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
+    "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
+    "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
+    "omo_eval_grad_columns": (ci, [_vp, _dp, _ip, ci, cd, ci, ci, _vp, ci]),
+    "omo_grad_from_columns": (ci, [_dp, ci, cd, _dp, _dp]),
+    "omo_shard_range": (None, [ci, ci, ci, _ip, _ip]),
+    "omo_device_alloc": (ci, [_vp, _ull, C.POINTER(_vp)]),
+    "omo_device_free": (ci, [_vp, _vp]),
+    "omo_host_alloc_pinned": (ci, [_vp, _ull, C.POINTER(_vp)]),
+    "omo_host_free_pinned": (ci, [_vp, _vp]),
+    "omo_memcpy_h2d": (ci, [_vp, _vp, _vp, _ull]),
+    "omo_memcpy_d2h": (ci, [_vp, _vp, _vp, _ull]),
+    "omo_synchronize": (ci, [_vp]),
+    "omo_stream": (_vp, [_vp]),
+    "omo_set_counting": (ci, [_vp, ci]),
+    "omo_get_counters": (ci, [_vp, C.POINTER(_ull)]),
+    "omo_kernel_timing": (ci, [_vp, ci, _dp, _ip]),
+    "omo_measure_dfma_peak": (ci, [_vp, _dp]),
+}
+for _n, (_r, _a) in _OMO_SIG.items():
+    _sig(_omo, _n, _r, _a)
+
+
+def _d(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a, a.ctypes.data_as(_dp)
+
+
+def _i(a):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    return a, a.ctypes.data_as(_ip)
+
+
+def shard_range(n, rank, world):
+    b, c = C.c_int(0), C.c_int(0)
+    _omo.omo_shard_range(n, rank, world, C.byref(b), C.byref(c))
+    return b.value, c.value
+
+
+def grad_from_columns(f_cols, h):
+    f_cols, fp = _d(f_cols)
+    F = (f_cols.size - 1) // 2
+    g = np.zeros(F)
+    f0 = C.c_double(0.0)
+    _omo.omo_grad_from_columns(fp, F, float(h), C.byref(f0), g.ctypes.data_as(_dp))
+    return f0.value, g
+
+
+class Engine:
+    """Raw view of an omo_ctx* (include/omo.h) owned by a Core. Device-resident entry points for the harness."""
+
+    def __init__(self, handle):
+        if not handle:
+            raise EngineError("engine is not available: " + (_core.optimo_last_error() or b"").decode())
+        self.h = handle
+
+    def _ck(self, st, what):
+        if st != 0:
+            raise EngineError(f"{what}: status {st}: {(_omo.omo_last_error(self.h) or b'').decode()}")
+
+    @property
+    def num_samples(self):
+        return _omo.omo_num_samples(self.h)
+
+    @property
+    def D(self):
+        return _omo.omo_descriptor_size(self.h)
+
+    @property
+    def dof(self):
+        return _omo.omo_dof(self.h)
+
+    def time_grid(self):
+        t = np.zeros(self.num_samples)
+        self._ck(_omo.omo_get_time_grid(self.h, t.ctypes.data_as(_dp)), "omo_get_time_grid")
+        return t
+
+    def cost_weights(self):
+        w = np.zeros(self.num_samples)
+        self._ck(_omo.omo_get_cost_weights(self.h, w.ctypes.data_as(_dp)), "omo_get_cost_weights")
+        return w
+
+    def p_original(self):
+        p = np.zeros((self.num_samples, self.dof))
+        self._ck(_omo.omo_get_p_original(self.h, p.ctypes.data_as(_dp)), "omo_get_p_original")
+        return p
+
+    def eval(self, X, want_terms=False):
+        X, xp = _d(X)
+        X2 = X.reshape(-1, self.D)
+        f = np.zeros(X2.shape[0])
+        terms = np.zeros((X2.shape[0], 3)) if want_terms else None
+        self._ck(_omo.omo_eval(self.h, xp, X2.shape[0], f.ctypes.data_as(_dp), terms.ctypes.data_as(_dp) if want_terms else None), "omo_eval")
+        return (f, terms) if want_terms else f
+
+    def eval_host_ptr(self, x_ptr, B, f_ptr):
+        """omo_eval on caller-owned (e.g. pinned) host buffers given as integer addresses."""
+        self._ck(_omo.omo_eval(self.h, C.cast(x_ptr, _dp), B, C.cast(f_ptr, _dp), None), "omo_eval")
+
+    def eval_device(self, dX, B, dF, dTerms=None, sync=True):
+        self._ck(_omo.omo_eval_device(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device")
+
+    def eval_grad(self, x, free_idx, h=1e-4):
+        x, xp = _d(x)
+        idx, ip = _i(free_idx)
+        g, fpm = np.zeros(idx.size), np.zeros((idx.size, 2))
+        f0 = C.c_double(0.0)
+        self._ck(_omo.omo_eval_grad(self.h, xp, ip, idx.size, float(h), C.byref(f0), g.ctypes.data_as(_dp), fpm.ctypes.data_as(_dp)), "omo_eval_grad")
+        return f0.value, g, fpm
+
+    def eval_grad_columns(self, x, free_idx, h, col_begin, col_count, d_out, sync=True):
+        x, xp = _d(x)
+        idx, ip = _i(free_idx)
+        self._ck(_omo.omo_eval_grad_columns(self.h, xp, ip, idx.size, float(h), col_begin, col_count, d_out, int(sync)), "omo_eval_grad_columns")
+
+    def device_alloc(self, nbytes):
+        p = _vp()
+        self._ck(_omo.omo_device_alloc(self.h, nbytes, C.byref(p)), "omo_device_alloc")
+        return p.value
+
+    def device_free(self, p):
+        self._ck(_omo.omo_device_free(self.h, p), "omo_device_free")
+
+    def pinned_alloc(self, nbytes):
+        p = _vp()
+        self._ck(_omo.omo_host_alloc_pinned(self.h, nbytes, C.byref(p)), "omo_host_alloc_pinned")
+        return p.value
+
+    def pinned_free(self, p):
+        self._ck(_omo.omo_host_free_pinned(self.h, p), "omo_host_free_pinned")
+
+    def pinned_array(self, shape):
+        """numpy view over freshly allocated pinned host memory (freed with pinned_free(arr.ctypes.data))."""
+        n = int(np.prod(shape))
+        p = self.pinned_alloc(n * 8)
+        buf = (C.c_double * n).from_address(p)
+        return np.frombuffer(buf, dtype=np.float64).reshape(shape)
+
+    def h2d(self, dst, arr):
+        arr = np.ascontiguousarray(arr)
+        self._ck(_omo.omo_memcpy_h2d(self.h, dst, arr.ctypes.data, arr.nbytes), "omo_memcpy_h2d")
+
+    def d2h(self, src, shape, dtype=np.float64):
+        out = np.zeros(shape, dtype=dtype)
+        self._ck(_omo.omo_memcpy_d2h(self.h, out.ctypes.data, src, out.nbytes), "omo_memcpy_d2h")
+        return out
+
+    def synchronize(self):
+        self._ck(_omo.omo_synchronize(self.h), "omo_synchronize")
+
+    def stream(self):
+        return _omo.omo_stream(self.h)
+
+    def set_counting(self, on):
+        self._ck(_omo.omo_set_counting(self.h, int(on)), "omo_set_counting")
+
+    def counters(self):
+        out = (_ull * 5)()
+        self._ck(_omo.omo_get_counters(self.h, out), "omo_get_counters")
+        return {"bezier_evals": out[0], "newton_iters": out[1], "ik_solves": out[2], "ik_iters": out[3], "launches": out[4]}
+
+    def kernel_timing(self, reset=0):
+        ms, n = C.c_double(0.0), C.c_int(0)
+        self._ck(_omo.omo_kernel_timing(self.h, int(reset), C.byref(ms), C.byref(n)), "omo_kernel_timing")
+        return ms.value, n.value
+
+    def dfma_peak(self):
+        v = C.c_double(0.0)
+        self._ck(_omo.omo_measure_dfma_peak(self.h, C.byref(v)), "omo_measure_dfma_peak")
+        return v.value
+
+
+class Core:
+    """Headless Core (one instance == one scene + one lazily created GPU engine)."""
+
+    def __init__(self, scene=None, device=None):
+        self.h = _core.optimo_core_new()
+        if not self.h:
+            raise EngineError("optimo_core_new failed")
+        if device is not None:
+            self._ck(_core.optimo_set_device(self.h, int(device)))
+        if scene is not None:
+            if isinstance(scene, dict):
+                self.ReadJsonString(json.dumps(scene))
+            else:
+                self.ReadJson(scene)
+
+    def __del__(self):
+        try:
+            if self.h:
+                _core.optimo_core_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc == 0:
+            return
+        msg = (_core.optimo_last_error() or b"").decode()
+        if rc == 2:
+            raise ForcedStop(msg)
+        raise EngineError(msg)
+
+    # ---- IO / structure ------------------------------------------------------------------------------
+    def ReadJson(self, path):
+        self._ck(_core.optimo_read_json(self.h, os.fspath(path).encode()))
+
+    def ReadJsonString(self, text):
+        self._ck(_core.optimo_read_json_string(self.h, text.encode()))
+
+    def WriteJson(self, path):
+        self._ck(_core.optimo_write_json(self.h, os.fspath(path).encode()))
+
+    def scene_json(self):
+        n = _core.optimo_scene_json(self.h, None, 0)
+        buf = C.create_string_buffer(n + 1)
+        _core.optimo_scene_json(self.h, buf, n + 1)
+        return buf.value.decode()
+
+    @property
+    def min_frame_(self):
+        return _core.optimo_min_frame(self.h)
+
+    @property
+    def max_frame_(self):
+        return _core.optimo_max_frame(self.h)
+
+    @property
+    def window(self):
+        """[min_frame - 2, max_frame + 2], the objective window of PerformOptimization (core_opt.cpp:125-126)."""
+        return self.min_frame_ - 2.0, self.max_frame_ + 2.0
+
+    @property
+    def J(self):
+        return _core.optimo_num_joints(self.h)
+
+    @property
+    def D(self):
+        return _core.optimo_descriptor_size(self.h)
+
+    def item_names(self):
+        out = []
+        buf = C.create_string_buffer(256)
+        for k in range(_core.optimo_num_items(self.h)):
+            _core.optimo_item_name(self.h, k, buf, 256)
+            out.append(buf.value.decode())
+        return out
+
+    def GetDescriptor(self):
+        x = np.zeros(self.D)
+        self._ck(_core.optimo_get_descriptor(self.h, x.ctypes.data_as(_dp)))
+        return x
+
+    def SetDescriptor(self, x):
+        a, p = _d(x)
+        self._ck(_core.optimo_set_descriptor(self.h, p, a.size))
+
+    def set_cyclic(self, flag):
+        _core.optimo_set_cyclic(self.h, int(bool(flag)))
+
+    def joint_physical(self, joint):
+        out = np.zeros(13)
+        self._ck(_core.optimo_joint_physical(self.h, joint, out.ctypes.data_as(_dp)))
+        return out[0], out[1:4].copy(), out[4:13].reshape(3, 3).copy()
+
+    # ---- runtime state -------------------------------------------------------------------------------
+    def UpdateOriginalParameters(self, x):
+        a, p = _d(x)
+        self._ck(_core.optimo_update_original_parameters(self.h, p, a.size))
+
+    def RetrieveOriginalParameters(self):
+        x = np.zeros(self.D)
+        self._ck(_core.optimo_retrieve_original_parameters(self.h, x.ctypes.data_as(_dp)))
+        return x
+
+    def UpdateGlobalWeight(self, w):
+        _core.optimo_update_global_weight(self.h, float(w))
+
+    def UpdatePerItemWeight(self, w, item_name):
+        self._ck(_core.optimo_update_per_item_weight(self.h, float(w), item_name.encode()))
+
+    def set_kernels(self, kernels):
+        _core.optimo_clear_kernels(self.h)
+        for amp, mu, sigma in kernels:
+            _core.optimo_add_kernel(self.h, float(amp), float(mu), float(sigma))
+
+    def GetCostWeight(self, t):
+        return _core.optimo_get_cost_weight(self.h, float(t))
+
+    def CalculateParameterWeights(self):
+        w = np.zeros(self.D)
+        self._ck(_core.optimo_parameter_weights(self.h, w.ctypes.data_as(_dp)))
+        return w
+
+    def select_items(self, names):
+        for n in self.item_names():
+            self._ck(_core.optimo_set_selected(self.h, n.encode(), int(n in names)))
+        _core.optimo_update_freezed_dofs_from_selection(self.h)
+
+    @property
+    def freezed_dofs_(self):
+        f = np.zeros(self.D, dtype=np.int32)
+        _core.optimo_get_freezed_dofs(self.h, f.ctypes.data_as(_ip))
+        return f
+
+    @freezed_dofs_.setter
+    def freezed_dofs_(self, f):
+        a, p = _i(f)
+        self._ck(_core.optimo_set_freezed_dofs(self.h, p, a.size))
+
+    def free_indices(self):
+        return np.nonzero(self.freezed_dofs_ == 0)[0].astype(np.int32)
+
+    # ---- the hot path --------------------------------------------------------------------------------
+    def CalculateFullObjective(self, min_t, max_t, x, x_original, want_terms=False):
+        xa, xp = _d(x)
+        oa, op = _d(x_original)
+        f = C.c_double(0.0)
+        terms = np.zeros(3)
+        self._ck(_core.optimo_calculate_full_objective(self.h, min_t, max_t, xp, op, xa.size, C.byref(f), terms.ctypes.data_as(_dp)))
+        return (f.value, terms) if want_terms else f.value
+
+    def CalculateFullObjectiveBatch(self, min_t, max_t, X, x_original, want_terms=False):
+        oa, op = _d(x_original)
+        Xa, Xp = _d(X)
+        Xa = Xa.reshape(-1, oa.size)
+        f = np.zeros(Xa.shape[0])
+        terms = np.zeros((Xa.shape[0], 3)) if want_terms else None
+        self._ck(_core.optimo_calculate_full_objective_batch(self.h, min_t, max_t, Xp, Xa.shape[0], op, oa.size, f.ctypes.data_as(_dp),
+                                                            terms.ctypes.data_as(_dp) if want_terms else None))
+        return (f, terms) if want_terms else f
+
+    def CalculateGradient(self, min_t, max_t, x, x_original, free_idx=None, h=1e-4):
+        """Returns (f0, grad[F], fpm[F,2])."""
+        xa, xp = _d(x)
+        oa, op = _d(x_original)
+        idx, ip = _i(self.free_indices() if free_idx is None else free_idx)
+        g, fpm = np.zeros(idx.size), np.zeros((idx.size, 2))
+        f0 = C.c_double(0.0)
+        self._ck(_core.optimo_calculate_gradient(self.h, min_t, max_t, xp, op, xa.size, ip, idx.size, float(h), C.byref(f0),
+                                                g.ctypes.data_as(_dp), fpm.ctypes.data_as(_dp)))
+        return f0.value, g, fpm
+
+    def positions(self, min_t, max_t, x):
+        xa, xp = _d(x)
+        n = _core.optimo_num_samples(self.h, min_t, max_t)
+        p = np.zeros((n, 3 * self.J))
+        self._ck(_core.optimo_positions(self.h, min_t, max_t, xp, xa.size, p.ctypes.data_as(_dp)))
+        return p
+
+    def EvaluateObjective(self, x_free, x_initial, min_t=None, max_t=None, want_gradient=False, h=1e-4):
+        lo, hi = self.window
+        min_t = lo if min_t is None else min_t
+        max_t = hi if max_t is None else max_t
+        xa, xp = _d(x_free)
+        ia, ip = _d(x_initial)
+        f = C.c_double(0.0)
+        g = np.zeros(xa.size) if want_gradient else None
+        self._ck(_core.optimo_evaluate_objective(self.h, xp, xa.size, ip, ia.size, min_t, max_t, int(want_gradient), float(h), C.byref(f),
+                                                g.ctypes.data_as(_dp) if want_gradient else None))
+        return (f.value, g) if want_gradient else f.value
+
+    @property
+    def stop_optimization_(self):
+        return bool(_core.optimo_get_stop_optimization(self.h))
+
+    @stop_optimization_.setter
+    def stop_optimization_(self, flag):
+        _core.optimo_set_stop_optimization(self.h, int(bool(flag)))
+
+    def PerformOptimization(self, explicit_termination=False):
+        """Returns (final objective value, function evaluations)."""
+        v, n = C.c_double(0.0), C.c_int(0)
+        self._ck(_core.optimo_perform_optimization(self.h, int(explicit_termination), C.byref(v), C.byref(n)))
+        return v.value, n.value
+
+    def GetOptimizationCache(self):
+        n, dof = C.c_int(0), C.c_int(0)
+        self._ck(_core.optimo_cache_size(self.h, C.byref(n), C.byref(dof)))
+        out = {}
+        for which, (name, width) in enumerate([("time", 0), ("q", dof.value), ("qd", dof.value), ("qdd", dof.value), ("tau", dof.value), ("local_cost", 0)]):
+            a = np.zeros((n.value, width)) if width else np.zeros(n.value)
+            self._ck(_core.optimo_get_cache(self.h, which, a.ctypes.data_as(_dp)))
+            out[name] = a
+        return out
+
+    def ClearOptimizationCache(self):
+        _core.optimo_clear_optimization_cache(self.h)
+
+    def engine(self, synced_window=None):
+        """The omo_ctx behind this Core. With `synced_window=(min_t, max_t)` the window / weights / x_original
+        are pushed first (by one evaluation of the current descriptor)."""
+        if synced_window is None:
+            h = _core.optimo_engine(self.h)
+        else:
+            h = _core.optimo_engine_synced(self.h, float(synced_window[0]), float(synced_window[1]))
+        return Engine(h)

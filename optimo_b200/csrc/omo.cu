@@ -1,0 +1,810 @@
+// libomo.so -- C ABI (include/omo.h) over the sm_100a kernels in omo_kernels.cuh / omo_objective.cuh.
+// Host side of the CUDA library only: scene-table flattening for constant memory, buffer management, launches.
+// No CPU implementation of the objective lives here: without a CUDA device every entry point fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "omo_objective.cuh"
+
+namespace {
+
+std::string g_create_error;
+std::mutex g_scene_mutex;
+const omo_ctx* g_active_scene[64] = {nullptr};  // per device: whose table sits in c_scene
+
+constexpr int kBlockThreads = 128;
+
+}  // namespace
+
+struct omo_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // scene
+    int J = 0, n_ik = 0, n_cp = 0, D = 0, n_channels = 0;
+    OmoDevScene hs;               // host copy of the constant table
+    bool scene_dirty = true;      // hs changed since the last upload
+    std::vector<int> cp_of_pos, first_of_pos, last_of_pos, next_same;
+    std::vector<double> joint_const_q;  // dynamics q of constant channels (for residues)
+    int *d_cp_of_pos = nullptr, *d_first_of_pos = nullptr, *d_last_of_pos = nullptr, *d_next_same = nullptr;
+    int n_slots_nofk = 0, n_slots_fk = 0;
+
+    // window
+    bool have_window = false;
+    double min_t = 0, max_t = 0, dt = 0.2;
+    std::vector<double> tgrid;
+    int N_s = 0, n_tiles = 0, T_out = 0;
+    double* d_tgrid = nullptr;
+
+    // weights
+    bool have_weights = false;
+    std::vector<double> wparam;
+    std::vector<omo_gauss> kernels;
+    double w_traj = 0.0;
+    int cyclic = 0;
+    std::vector<double> wcost;
+    double *d_wparam = nullptr, *d_wcost = nullptr;
+    bool wcost_dirty = true;
+
+    // original motion
+    bool have_original = false;
+    std::vector<double> x0;
+    double *d_x0 = nullptr, *d_p_orig = nullptr;  // d_p_orig: [3J][N_s]
+    bool p_orig_dirty = true;
+
+    // work buffers (capacity in candidates)
+    int cap = 0;
+    double *d_X = nullptr, *d_prep = nullptr, *d_dparam = nullptr, *d_partial = nullptr, *d_f = nullptr, *d_terms = nullptr;
+    unsigned* d_flags = nullptr;
+    // single-candidate outputs (OptimizationCache)
+    double *d_oq = nullptr, *d_oqd = nullptr, *d_oqdd = nullptr, *d_otau = nullptr, *d_olocal = nullptr, *d_op = nullptr;
+    int out_cap_samples = 0;
+    // gradient scratch
+    double* d_xbase = nullptr; int* d_free = nullptr; int free_cap = 0;
+    std::vector<double> h_cols;
+
+    // counters / timing
+    unsigned long long* d_counters = nullptr;
+    bool counting = false;
+    unsigned long long launches = 0;
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timed;
+    std::vector<cudaEvent_t> event_pool;
+};
+
+namespace {
+
+#define OMO_CUDA(call)                                                                                     \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) {                                                                           \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+            return (e_ == cudaErrorMemoryAllocation) ? OMO_OOM : OMO_CUDA_ERROR;                           \
+        }                                                                                                  \
+    } while (0)
+
+omo_status fail(omo_ctx* ctx, omo_status st, const std::string& msg)
+{
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+    return st;
+}
+
+template <typename T> omo_status dev_alloc(omo_ctx* ctx, T** p, size_t n)
+{
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    if (n == 0) n = 1;
+    OMO_CUDA(cudaMalloc((void**)p, n * sizeof(T)));
+    return OMO_OK;
+}
+
+template <typename T> omo_status upload(omo_ctx* ctx, T** p, const std::vector<T>& v)
+{
+    omo_status st = dev_alloc(ctx, p, v.size());
+    if (st != OMO_OK) return st;
+    if (!v.empty()) OMO_CUDA(cudaMemcpyAsync(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    return OMO_OK;
+}
+
+// SpatialRigidBodyInertia::createFromMassComInertiaC (external/rbdl-v2.5.0/include/rbdl/SpatialAlgebraOperators.h:116-128):
+// I = inertia_C + m * (cx * cx^T), h = m * com.
+void make_body(OmoBody& B, const double* r, double mass, const double* com, const double* Ic)
+{
+    B.r[0] = r[0]; B.r[1] = r[1]; B.r[2] = r[2];
+    B.m = mass;
+    B.h[0] = com[0] * mass; B.h[1] = com[1] * mass; B.h[2] = com[2] * mass;
+    double cx[3][3] = {{0.0, -com[2], com[1]}, {com[2], 0.0, -com[0]}, {-com[1], com[0], 0.0}};
+    double I[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            const double cc = cx[i][0] * cx[j][0] + cx[i][1] * cx[j][1] + cx[i][2] * cx[j][2];
+            I[i][j] = Ic[3 * i + j] + cc * mass;
+        }
+    B.Ixx = I[0][0]; B.Iyx = I[1][0]; B.Iyy = I[1][1]; B.Izx = I[2][0]; B.Izy = I[2][1]; B.Izz = I[2][2];
+}
+
+// Rounding residue the 5-point stencils leave on a constant channel (core_rbdl.cpp:49,84; SURVEY §7 ix).
+void constant_residue(double c, double dx, double* qd, double* qdd)
+{
+    volatile double v = c;  // keep the reference's left-to-right evaluation
+    *qd = (-v + 8.0 * v - 8.0 * v + v) / (12.0 * dx);
+    *qdd = (-v + 16.0 * v - 30.0 * v + 16.0 * v - v) / (12.0 * dx * dx);
+}
+
+omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
+{
+    const int J = sc->n_joints;
+    if (J < 1 || J > OMO_MAXJ) return fail(ctx, OMO_BAD_ARG, "n_joints must be in [1, OMO_MAX_JOINTS]");
+    if (sc->n_ik < 0 || sc->n_ik > OMO_MAX_IK) return fail(ctx, OMO_BAD_ARG, "n_ik must be in [0, OMO_MAX_IK]");
+    if (sc->n_channels != 3 * J + 3 * sc->n_ik) return fail(ctx, OMO_BAD_ARG, "n_channels must equal 3*J + 3*n_ik");
+    if (!sc->parent || !sc->offset || !sc->mass || !sc->com || !sc->inertia || !sc->chan_const || !sc->chan_first_cp || !sc->chan_n_cp)
+        return fail(ctx, OMO_BAD_ARG, "null scene table");
+    if (sc->n_cp > 0 && !sc->chain) return fail(ctx, OMO_BAD_ARG, "null chain table");
+    if (sc->parent[0] != -1) return fail(ctx, OMO_BAD_ARG, "parent[0] must be -1 (root first)");
+    OmoDevScene& S = ctx->hs;
+    std::memset(&S, 0, sizeof(S));
+    S.J = J; S.n_ik = sc->n_ik;
+    ctx->J = J; ctx->n_ik = sc->n_ik; ctx->n_cp = sc->n_cp; ctx->D = 5 * sc->n_cp; ctx->n_channels = sc->n_channels;
+
+    std::vector<int> depth(J, 0), nchild(J, 0);
+    for (int j = 1; j < J; ++j) {
+        const int p = sc->parent[j];
+        if (p < 0 || p >= j) return fail(ctx, OMO_BAD_ARG, "joints must be in DFS pre-order (0 <= parent[j] < j)");
+        depth[j] = depth[p] + 1;
+        nchild[p] += 1;
+    }
+    // DFS pre-order check: parent[j] must be j-1 or an ancestor of j-1
+    for (int j = 2; j < J; ++j) {
+        int k = j - 1; bool ok = false;
+        while (k >= 0) { if (k == sc->parent[j]) { ok = true; break; } k = sc->parent[k]; }
+        if (!ok) return fail(ctx, OMO_BAD_ARG, "joints are not in DFS pre-order");
+    }
+    // stack plan: (f, sincos) by depth for open non-leaf bodies; (v, a) and (L, t) by number of branching ancestors
+    int max_fs = 0, max_va = 0, max_fk = 0;
+    std::vector<int> nbranch_nonroot(J, 0), nbranch_all(J, 0);
+    for (int j = 0; j < J; ++j) {
+        S.parent[j] = sc->parent[j];
+        S.n_child[j] = (unsigned char)std::min(nchild[j], 255);
+        if (j > 0) {
+            const int p = sc->parent[j];
+            nbranch_nonroot[j] = nbranch_nonroot[p] + ((p > 0 && nchild[p] >= 2) ? 1 : 0);
+            nbranch_all[j] = nbranch_all[p] + ((nchild[p] >= 2) ? 1 : 0);
+        }
+        S.fs_slot[j] = -1; S.va_slot[j] = -1; S.fk_slot[j] = -1;
+        if (j > 0 && nchild[j] > 0) { S.fs_slot[j] = (short)(depth[j] - 1); max_fs = std::max(max_fs, depth[j]); }
+        if (j > 0 && nchild[j] >= 2) { S.va_slot[j] = (short)nbranch_nonroot[j]; max_va = std::max(max_va, nbranch_nonroot[j] + 1); }
+        if (nchild[j] >= 2) { S.fk_slot[j] = (short)nbranch_all[j]; max_fk = std::max(max_fk, nbranch_all[j] + 1); }
+    }
+    for (int j = 0; j < J; ++j) {
+        if (S.va_slot[j] >= 0) S.va_slot[j] = (short)(S.va_slot[j] + max_fs);
+        if (S.fk_slot[j] >= 0) S.fk_slot[j] = (short)(S.fk_slot[j] + max_fs + max_va);
+    }
+    ctx->n_slots_nofk = max_fs + max_va;
+    ctx->n_slots_fk = max_fs + max_va + max_fk;
+    S.n_slots = ctx->n_slots_fk;
+
+    // bodies (core_rbdl.cpp:228-252): body j hangs at Xtrans(parent.offset), carries j's own mass properties
+    for (int j = 0; j < J; ++j) {
+        for (int k = 0; k < 3; ++k) S.offset[j][k] = sc->offset[3 * j + k];
+        if (j == 0) { const double z[3] = {0, 0, 0}; const double zi[9] = {0}; make_body(S.body[0], sc->offset, 0.0, z, zi); continue; }
+        make_body(S.body[j], sc->offset + 3 * sc->parent[j], sc->mass[j], sc->com + 3 * j, sc->inertia + 9 * j);
+    }
+
+    // channels -> chain-ordered positions
+    ctx->cp_of_pos.assign(sc->n_cp, 0); ctx->first_of_pos.assign(sc->n_cp, 0); ctx->last_of_pos.assign(sc->n_cp, 0);
+    ctx->next_same.assign(sc->n_cp, 0);
+    int pos = 0;
+    for (int ch = 0; ch < sc->n_channels; ++ch) {
+        const int n = sc->chan_n_cp[ch], first = sc->chan_first_cp[ch];
+        if (n < 0 || (n > 0 && (first < 0 || first + n > sc->n_cp))) return fail(ctx, OMO_BAD_ARG, "bad channel control-point range");
+        int cpos = -1;
+        if (n > 0) {
+            if (first != pos) return fail(ctx, OMO_BAD_ARG, "channels must list their control points contiguously in descriptor order");
+            cpos = pos;
+            for (int i = 0; i < n; ++i) {
+                const int cp = sc->chain[first + i];
+                if (cp < first || cp >= first + n) return fail(ctx, OMO_BAD_ARG, "chain entry outside its channel");
+                ctx->cp_of_pos[pos] = cp; ctx->first_of_pos[pos] = first; ctx->last_of_pos[pos] = first + n - 1;
+                ctx->next_same[pos] = (i + 1 < n) ? 1 : 0;
+                ++pos;
+            }
+        }
+        if (ch < 3 * J) {
+            S.chan_pos[ch] = cpos; S.chan_n[ch] = n; S.chan_const[ch] = sc->chan_const[ch];
+            S.chan_sin[ch] = std::sin(sc->chan_const[ch]); S.chan_cos[ch] = std::cos(sc->chan_const[ch]);
+            if (n > 0) S.dyn[ch / 3] |= (unsigned char)(1 << (ch % 3));
+        } else {
+            const int h = (ch - 3 * J) / 3, a = (ch - 3 * J) % 3;
+            S.ik_chan_pos[h][a] = cpos; S.ik_chan_n[h][a] = n; S.ik_chan_const[h][a] = sc->chan_const[ch];
+        }
+    }
+    if (pos != sc->n_cp) return fail(ctx, OMO_BAD_ARG, "n_cp does not match the channels' control points");
+
+    // IK handlers (ikhandler.cpp:45-67,77-101): chain = path root .. end effector
+    for (int j = 0; j < J; ++j) { S.ik_of[j] = -1; S.ik_idx[j] = 0; S.ik_start[j] = -1; }
+    for (int h = 0; h < sc->n_ik; ++h) {
+        const int root = sc->ik_root[h], end = sc->ik_end[h];
+        if (root <= 0 || root >= J || end <= 0 || end >= J) return fail(ctx, OMO_BAD_ARG, "IK root/end must be non-root joints");
+        std::vector<int> path;
+        for (int j = end;; j = sc->parent[j]) {
+            path.insert(path.begin(), j);
+            if (j == root) break;
+            if (j <= 0) return fail(ctx, OMO_BAD_ARG, "IK end effector is not a descendant of the IK root");
+        }
+        const int nb = (int)path.size() - 1;
+        if (nb < 1 || nb > OMO_MAX_IK_CHAIN) return fail(ctx, OMO_BAD_ARG, "IK chain length must be in [1, OMO_MAX_IK_CHAIN]");
+        S.ik_nb[h] = nb;
+        for (int i = 0; i <= nb; ++i) S.ik_joint[h][i] = path[i];
+        S.ik_start[root] = (short)h;
+        for (int i = 0; i < nb; ++i) { S.ik_of[path[i]] = (short)h; S.ik_idx[path[i]] = (short)i; }
+    }
+    ctx->scene_dirty = true;
+    omo_status st;
+    if ((st = upload(ctx, &ctx->d_cp_of_pos, ctx->cp_of_pos)) != OMO_OK) return st;
+    if ((st = upload(ctx, &ctx->d_first_of_pos, ctx->first_of_pos)) != OMO_OK) return st;
+    if ((st = upload(ctx, &ctx->d_last_of_pos, ctx->last_of_pos)) != OMO_OK) return st;
+    if ((st = upload(ctx, &ctx->d_next_same, ctx->next_same)) != OMO_OK) return st;
+    return OMO_OK;
+}
+
+void refresh_residues(omo_ctx* ctx)
+{
+    OmoDevScene& S = ctx->hs;
+    for (int ch = 0; ch < 3 * ctx->J; ++ch) constant_residue(S.chan_const[ch], ctx->dt, &S.chan_qd[ch], &S.chan_qdd[ch]);
+    for (int k = 0; k < 3; ++k) constant_residue(S.offset[0][k], ctx->dt, &S.root_qd[k], &S.root_qdd[k]);
+    ctx->scene_dirty = true;
+}
+
+omo_status activate_scene(omo_ctx* ctx)
+{
+    std::lock_guard<std::mutex> g(g_scene_mutex);
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return fail(ctx, OMO_BAD_ARG, "device index out of range");
+    if (g_active_scene[dev] == ctx && !ctx->scene_dirty) return OMO_OK;
+    if (g_active_scene[dev] != nullptr && g_active_scene[dev] != ctx) OMO_CUDA(cudaDeviceSynchronize());  // other ctx may still read it
+    OMO_CUDA(cudaMemcpyToSymbolAsync(c_scene, &ctx->hs, sizeof(OmoDevScene), 0, cudaMemcpyHostToDevice, ctx->stream));
+    g_active_scene[dev] = ctx;
+    ctx->scene_dirty = false;
+    return OMO_OK;
+}
+
+omo_status ensure_capacity(omo_ctx* ctx, int B)
+{
+    if (B <= ctx->cap) return OMO_OK;
+    const int cap = std::max(B, 16);
+    omo_status st;
+    if ((st = dev_alloc(ctx, &ctx->d_X, (size_t)cap * ctx->D)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_prep, (size_t)cap * 6 * ctx->n_cp)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_dparam, (size_t)cap)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_flags, (size_t)cap)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_partial, (size_t)cap * std::max(ctx->n_tiles, 1) * 2)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_f, (size_t)cap)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_terms, (size_t)cap * 3)) != OMO_OK) return st;
+    ctx->cap = cap;
+    return OMO_OK;
+}
+
+size_t smem_bytes(const omo_ctx* ctx, bool fk)
+{
+    const int slots = fk ? ctx->n_slots_fk : ctx->n_slots_nofk;
+    return (size_t)(6 + slots * OMO_SLOT) * kBlockThreads * sizeof(double);
+}
+
+template <bool FK, bool IK, bool OUT>
+omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B)
+{
+    const size_t smem = std::max(smem_bytes(ctx, FK), (size_t)64 * sizeof(double));
+    if (smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
+    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<FK, IK, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->timing && !OUT) {
+        OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
+        OMO_CUDA(cudaEventRecord(e0, ctx->stream));
+    }
+    omo::objective_kernel<FK, IK, OUT><<<B * ctx->n_tiles, kBlockThreads, smem, ctx->stream>>>(P);
+    OMO_CUDA(cudaGetLastError());
+    if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
+    ctx->launches += 1;
+    return OMO_OK;
+}
+
+omo_status launch_objective(omo_ctx* ctx, const OmoEvalParams& P, int B, bool fk, bool out)
+{
+    const bool ik = ctx->n_ik > 0;
+    if (ik) fk = true;
+    if (out) return ik ? launch_objective_t<true, true, true>(ctx, P, B) : launch_objective_t<true, false, true>(ctx, P, B);
+    if (ik) return launch_objective_t<true, true, false>(ctx, P, B);
+    return fk ? launch_objective_t<true, false, false>(ctx, P, B) : launch_objective_t<false, false, false>(ctx, P, B);
+}
+
+void fill_params(const omo_ctx* ctx, OmoEvalParams& P)
+{
+    std::memset(&P, 0, sizeof(P));
+    P.prep = ctx->d_prep; P.flags = ctx->d_flags; P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = ctx->d_partial;
+    P.N_s = ctx->N_s; P.n_tiles = ctx->n_tiles; P.T_out = ctx->T_out; P.n_cp = ctx->n_cp;
+    const double dt = ctx->dt;
+    P.dt = dt; P.inv_dt = 1.0 / dt; P.inv_2dt = 1.0 / (2.0 * dt); P.inv_12dt = 1.0 / (12.0 * dt);
+    P.inv_dt2 = 1.0 / (dt * dt); P.inv_2dt2 = 1.0 / (2.0 * dt * dt); P.inv_12dt2 = 1.0 / (12.0 * dt * dt);
+    P.w_traj = ctx->w_traj;
+    P.counters = ctx->counting ? ctx->d_counters : nullptr;
+}
+
+omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
+{
+    omo::OmoPrepParams Q;
+    Q.X = dX; Q.x0 = ctx->d_x0; Q.wparam = ctx->d_wparam;
+    Q.cp_of_pos = ctx->d_cp_of_pos; Q.first_of_pos = ctx->d_first_of_pos; Q.last_of_pos = ctx->d_last_of_pos; Q.next_same = ctx->d_next_same;
+    Q.prep = ctx->d_prep; Q.flags = ctx->d_flags; Q.dparam = ctx->d_dparam;
+    Q.n_cp = ctx->n_cp; Q.D = ctx->D; Q.cyclic = ctx->cyclic;
+    omo::prepare_kernel<<<B, 128, 0, ctx->stream>>>(Q);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return OMO_OK;
+}
+
+omo_status ensure_outputs(omo_ctx* ctx)
+{
+    if (ctx->out_cap_samples >= ctx->N_s && ctx->d_oq) return OMO_OK;
+    const size_t n = (size_t)ctx->N_s * 3 * ctx->J;
+    omo_status st;
+    if ((st = dev_alloc(ctx, &ctx->d_oq, n)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_oqd, n)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_oqdd, n)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_otau, n)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_op, n)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_olocal, (size_t)ctx->N_s)) != OMO_OK) return st;
+    ctx->out_cap_samples = ctx->N_s;
+    return OMO_OK;
+}
+
+// One candidate with per-sample outputs (used for the OptimizationCache, positions and p_original).
+omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig)
+{
+    omo_status st;
+    if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
+    if ((st = ensure_outputs(ctx)) != OMO_OK) return st;
+    if ((st = activate_scene(ctx)) != OMO_OK) return st;
+    if ((st = run_prepare(ctx, d_x, 1)) != OMO_OK) return st;
+    OmoEvalParams P;
+    fill_params(ctx, P);
+    P.p_orig = with_p_orig ? ctx->d_p_orig : nullptr;
+    P.o_q = ctx->d_oq; P.o_qd = ctx->d_oqd; P.o_qdd = ctx->d_oqdd; P.o_tau = ctx->d_otau; P.o_local = ctx->d_olocal; P.o_p = ctx->d_op;
+    if ((st = launch_objective(ctx, P, 1, true, true)) != OMO_OK) return st;
+    omo::finish_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, 1, ctx->n_tiles, ctx->d_f, ctx->d_terms);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return OMO_OK;
+}
+
+omo_status ensure_ready(omo_ctx* ctx)
+{
+    if (!ctx->have_window) return fail(ctx, OMO_NOT_READY, "omo_set_window has not been called");
+    if (!ctx->have_weights) return fail(ctx, OMO_NOT_READY, "omo_set_weights has not been called");
+    if (!ctx->have_original) return fail(ctx, OMO_NOT_READY, "omo_set_original has not been called");
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    omo_status st;
+    if (ctx->wcost_dirty) {
+        // Core::GetCostWeight (core.cpp:191-199) on the host's libm, exactly as the reference evaluates it
+        ctx->wcost.resize(ctx->N_s);
+        for (int i = 0; i < ctx->N_s; ++i) {
+            double w = 1.0;
+            for (const omo_gauss& k : ctx->kernels) w -= k.amp * std::exp(-(ctx->tgrid[i] - k.mu) * (ctx->tgrid[i] - k.mu) / (2.0 * k.sigma * k.sigma));
+            ctx->wcost[i] = std::max(w, 0.0);
+        }
+        if ((st = upload(ctx, &ctx->d_wcost, ctx->wcost)) != OMO_OK) return st;
+        ctx->wcost_dirty = false;
+    }
+    if (ctx->p_orig_dirty) {
+        // OriginalMotionCache (core_rbdl.cpp:357-368): positions of x_original, kept transposed [3J][N_s]
+        if ((st = dev_alloc(ctx, &ctx->d_p_orig, (size_t)ctx->N_s * 3 * ctx->J)) != OMO_OK) return st;
+        if ((st = run_single_out(ctx, ctx->d_x0, false)) != OMO_OK) return st;
+        const int n = ctx->N_s * 3 * ctx->J;
+        omo::transpose_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_op, ctx->N_s, 3 * ctx->J, ctx->d_p_orig);
+        OMO_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        ctx->p_orig_dirty = false;
+    }
+    return activate_scene(ctx);
+}
+
+omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, double* d_terms)
+{
+    omo_status st;
+    if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
+    if ((st = run_prepare(ctx, dX, B)) != OMO_OK) return st;
+    OmoEvalParams P;
+    fill_params(ctx, P);
+    const bool fk = (ctx->w_traj != 0.0) || ctx->n_ik > 0;
+    P.p_orig = (ctx->w_traj != 0.0) ? ctx->d_p_orig : nullptr;
+    if ((st = launch_objective(ctx, P, B, fk, false)) != OMO_OK) return st;
+    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, ctx->n_tiles, d_f, d_terms);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return OMO_OK;
+}
+
+}  // namespace
+
+// =====================================================================================================
+extern "C" {
+
+const char* omo_version(void) { return "optimo-b200 0.1 (sm_100a)"; }
+
+const char* omo_last_error(const omo_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+omo_status omo_create(const omo_scene_desc* scene, int device, omo_ctx** out)
+{
+    if (!scene || !out) return fail(nullptr, OMO_BAD_ARG, "null argument");
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) return fail(nullptr, OMO_CUDA_ERROR, std::string("no usable CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return fail(nullptr, OMO_BAD_ARG, "device index out of range");
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, OMO_CUDA_ERROR, cudaGetErrorString(e));
+    omo_ctx* ctx = new omo_ctx();
+    ctx->device = device;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_error = cudaGetErrorString(e); delete ctx; return OMO_CUDA_ERROR;
+    }
+    omo_status st = build_scene(ctx, scene);
+    if (st == OMO_OK) {
+        cudaError_t e2 = cudaMalloc((void**)&ctx->d_counters, 4 * sizeof(unsigned long long));
+        if (e2 != cudaSuccess) { ctx->err = cudaGetErrorString(e2); st = OMO_CUDA_ERROR; }
+        else cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream);
+    }
+    if (st != OMO_OK) { g_create_error = ctx->err; omo_destroy(ctx); return st; }
+    *out = ctx;
+    return OMO_OK;
+}
+
+void omo_destroy(omo_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    {
+        std::lock_guard<std::mutex> g(g_scene_mutex);
+        if (ctx->device >= 0 && ctx->device < 64 && g_active_scene[ctx->device] == ctx) g_active_scene[ctx->device] = nullptr;
+    }
+    void* ptrs[] = {ctx->d_cp_of_pos, ctx->d_first_of_pos, ctx->d_last_of_pos, ctx->d_next_same, ctx->d_tgrid, ctx->d_wparam, ctx->d_wcost,
+                    ctx->d_x0, ctx->d_p_orig, ctx->d_X, ctx->d_prep, ctx->d_dparam, ctx->d_partial, ctx->d_f, ctx->d_terms, ctx->d_flags,
+                    ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+omo_status omo_set_window(omo_ctx* ctx, double min_t, double max_t, double dt)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    if (!(dt > 0.0) || !(max_t >= min_t)) return fail(ctx, OMO_BAD_ARG, "need dt > 0 and max_t >= min_t");
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->have_window && ctx->min_t == min_t && ctx->max_t == max_t && ctx->dt == dt) return OMO_OK;
+    std::vector<double> grid;
+    for (double t = min_t; t <= max_t; t += dt) {  // core_rbdl.cpp:120-123 -- accumulated, never closed-form
+        grid.push_back(t);
+        if (grid.size() > (size_t)(1 << 24)) return fail(ctx, OMO_BAD_ARG, "time grid too long");
+    }
+    if (grid.size() < 3) return fail(ctx, OMO_BAD_ARG, "the window must hold at least 3 samples");
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->tgrid.swap(grid);
+    ctx->N_s = (int)ctx->tgrid.size();
+    ctx->min_t = min_t; ctx->max_t = max_t; ctx->dt = dt;
+    const int t_max = kBlockThreads - 4;
+    ctx->n_tiles = (ctx->N_s + t_max - 1) / t_max;
+    ctx->T_out = (ctx->N_s + ctx->n_tiles - 1) / ctx->n_tiles;
+    omo_status st = upload(ctx, &ctx->d_tgrid, ctx->tgrid);
+    if (st != OMO_OK) return st;
+    refresh_residues(ctx);
+    ctx->have_window = true;
+    ctx->wcost_dirty = true; ctx->p_orig_dirty = true;
+    ctx->cap = 0;  // partial[] depends on n_tiles
+    ctx->out_cap_samples = 0;
+    return OMO_OK;
+}
+
+omo_status omo_set_weights(omo_ctx* ctx, const double* w_param, int D, double w_traj, const omo_gauss* kernels, int n_kernels, int cyclic)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    if (D != ctx->D || (D > 0 && !w_param) || n_kernels < 0 || (n_kernels > 0 && !kernels)) return fail(ctx, OMO_BAD_ARG, "bad weights");
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    const bool same_param = ctx->have_weights && std::equal(w_param, w_param + D, ctx->wparam.begin());
+    if (!same_param) {
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->wparam.assign(w_param, w_param + D);
+        omo_status st = upload(ctx, &ctx->d_wparam, ctx->wparam);
+        if (st != OMO_OK) return st;
+    }
+    bool same_k = ctx->have_weights && (int)ctx->kernels.size() == n_kernels;
+    for (int i = 0; same_k && i < n_kernels; ++i)
+        same_k = kernels[i].amp == ctx->kernels[i].amp && kernels[i].mu == ctx->kernels[i].mu && kernels[i].sigma == ctx->kernels[i].sigma;
+    if (!same_k) { ctx->kernels.assign(kernels, kernels + n_kernels); ctx->wcost_dirty = true; }
+    ctx->w_traj = w_traj;
+    ctx->cyclic = cyclic ? 1 : 0;
+    ctx->have_weights = true;
+    return OMO_OK;
+}
+
+omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    if (D != ctx->D || (D > 0 && !x_original)) return fail(ctx, OMO_BAD_ARG, "bad x_original");
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    if (ctx->have_original && std::equal(x_original, x_original + D, ctx->x0.begin())) return OMO_OK;
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->x0.assign(x_original, x_original + D);
+    omo_status st = upload(ctx, &ctx->d_x0, ctx->x0);
+    if (st != OMO_OK) return st;
+    ctx->have_original = true;
+    ctx->p_orig_dirty = true;
+    return OMO_OK;
+}
+
+int omo_num_samples(const omo_ctx* ctx) { return ctx ? ctx->N_s : 0; }
+int omo_descriptor_size(const omo_ctx* ctx) { return ctx ? ctx->D : 0; }
+int omo_dof(const omo_ctx* ctx) { return ctx ? 3 * ctx->J : 0; }
+
+omo_status omo_get_time_grid(const omo_ctx* ctx, double* t_out)
+{
+    if (!ctx || !t_out || !ctx->have_window) return OMO_BAD_ARG;
+    std::copy(ctx->tgrid.begin(), ctx->tgrid.end(), t_out);
+    return OMO_OK;
+}
+
+omo_status omo_get_cost_weights(const omo_ctx* cctx, double* w_out)
+{
+    omo_ctx* ctx = const_cast<omo_ctx*>(cctx);
+    if (!ctx || !w_out) return OMO_BAD_ARG;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    std::copy(ctx->wcost.begin(), ctx->wcost.end(), w_out);
+    return OMO_OK;
+}
+
+omo_status omo_get_p_original(omo_ctx* ctx, double* p_out)
+{
+    if (!ctx || !p_out) return OMO_BAD_ARG;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    const int rows = 3 * ctx->J, cols = ctx->N_s;
+    std::vector<double> tmp((size_t)rows * cols);
+    OMO_CUDA(cudaMemcpyAsync(tmp.data(), ctx->d_p_orig, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < rows; ++r) for (int c = 0; c < cols; ++c) p_out[(size_t)c * rows + r] = tmp[(size_t)r * cols + c];
+    return OMO_OK;
+}
+
+omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync)
+{
+    if (!ctx || !dX || !d_f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (B == 0) return OMO_OK;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = eval_device_impl(ctx, dX, B, d_f_out, d_terms_out)) != OMO_OK) return st;
+    if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_terms* terms_out)
+{
+    if (!ctx || !X || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (B == 0) return OMO_OK;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, (size_t)B * ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
+    OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd, double* qdd,
+                           double* tau, double* local_cost)
+{
+    if (!ctx || !x) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    if ((st = run_single_out(ctx, ctx->d_X, ctx->w_traj != 0.0)) != OMO_OK) return st;
+    const size_t n = (size_t)ctx->N_s * 3 * ctx->J * sizeof(double);
+    if (q) OMO_CUDA(cudaMemcpyAsync(q, ctx->d_oq, n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (qd) OMO_CUDA(cudaMemcpyAsync(qd, ctx->d_oqd, n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (qdd) OMO_CUDA(cudaMemcpyAsync(qdd, ctx->d_oqdd, n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (tau) OMO_CUDA(cudaMemcpyAsync(tau, ctx->d_otau, n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (local_cost) OMO_CUDA(cudaMemcpyAsync(local_cost, ctx->d_olocal, (size_t)ctx->N_s * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (f_out) OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
+{
+    if (!ctx || !x || !p_out) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    if ((st = run_single_out(ctx, ctx->d_X, false)) != OMO_OK) return st;
+    OMO_CUDA(cudaMemcpyAsync(p_out, ctx->d_op, (size_t)ctx->N_s * 3 * ctx->J * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin, int col_count,
+                                 double* d_f_cols, int sync)
+{
+    if (!ctx || !x || (F > 0 && !free_idx) || F < 0 || !d_f_cols) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (col_begin < 0 || col_count < 0 || col_begin + col_count > 2 * F + 1) return fail(ctx, OMO_BAD_ARG, "column range outside [0, 2F+1)");
+    for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
+    if (col_count == 0) return OMO_OK;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, col_count)) != OMO_OK) return st;
+    if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
+    if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; }
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    if (F > 0) OMO_CUDA(cudaMemcpyAsync(ctx->d_free, free_idx, (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    omo::perturb_kernel<<<col_count, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    if ((st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr)) != OMO_OK) return st;
+    if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_grad_from_columns(const double* f_cols, int F, double h, double* f0_out, double* grad_out)
+{
+    if (!f_cols || F < 0 || (F > 0 && !grad_out)) return OMO_BAD_ARG;
+    if (f0_out) *f0_out = f_cols[0];
+    for (int k = 0; k < F; ++k) grad_out[k] = (f_cols[2 * k + 1] - f_cols[2 * k + 2]) / (2.0 * h);
+    return OMO_OK;
+}
+
+omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, double* f0_out, double* grad_out, double* fpm_out)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    const int P = 2 * F + 1;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, P)) != OMO_OK) return st;
+    if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
+    ctx->h_cols.resize(P);
+    OMO_CUDA(cudaMemcpyAsync(ctx->h_cols.data(), ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
+    return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
+}
+
+void omo_shard_range(int n, int rank, int world, int* begin, int* count)
+{
+    if (world < 1) world = 1;
+    const int base = n / world, rem = n % world;
+    const int b = rank * base + std::min(rank, rem);
+    if (begin) *begin = b;
+    if (count) *count = base + (rank < rem ? 1 : 0);
+}
+
+omo_status omo_device_alloc(omo_ctx* ctx, unsigned long long bytes, void** out)
+{
+    if (!ctx || !out) return OMO_BAD_ARG;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    OMO_CUDA(cudaMalloc(out, bytes ? bytes : 1));
+    return OMO_OK;
+}
+omo_status omo_device_free(omo_ctx* ctx, void* p)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    OMO_CUDA(cudaFree(p));
+    return OMO_OK;
+}
+omo_status omo_host_alloc_pinned(omo_ctx* ctx, unsigned long long bytes, void** out)
+{
+    if (!ctx || !out) return OMO_BAD_ARG;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    OMO_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    return OMO_OK;
+}
+omo_status omo_host_free_pinned(omo_ctx* ctx, void* p)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaFreeHost(p));
+    return OMO_OK;
+}
+omo_status omo_memcpy_h2d(omo_ctx* ctx, void* dst, const void* src, unsigned long long bytes)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+omo_status omo_memcpy_d2h(omo_ctx* ctx, void* dst, const void* src, unsigned long long bytes)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+omo_status omo_synchronize(omo_ctx* ctx)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+void* omo_stream(omo_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+omo_status omo_set_counting(omo_ctx* ctx, int enable)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    ctx->counting = enable != 0;
+    OMO_CUDA(cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    return OMO_OK;
+}
+
+omo_status omo_get_counters(omo_ctx* ctx, unsigned long long* out5)
+{
+    if (!ctx || !out5) return OMO_BAD_ARG;
+    OMO_CUDA(cudaMemcpyAsync(out5, ctx->d_counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    out5[4] = ctx->launches;
+    return OMO_OK;
+}
+
+omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* launches)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    double tot = 0.0;
+    for (auto& pr : ctx->timed) {
+        float ms = 0.f;
+        OMO_CUDA(cudaEventElapsedTime(&ms, pr.first, pr.second));
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = (int)ctx->timed.size();
+    if (reset) {
+        for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        ctx->timed.clear();
+        ctx->timing = reset > 0;  // reset = 1: (re)start timing; reset = -1: stop
+    }
+    return OMO_OK;
+}
+
+omo_status omo_measure_dfma_peak(omo_ctx* ctx, double* flops_per_s)
+{
+    if (!ctx || !flops_per_s) return OMO_BAD_ARG;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop;
+    OMO_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+    double* d_out = nullptr;
+    OMO_CUDA(cudaMalloc((void**)&d_out, (size_t)blocks * threads * sizeof(double)));
+    cudaEvent_t e0, e1;
+    OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 6; ++rep) {
+        OMO_CUDA(cudaEventRecord(e0, ctx->stream));
+        omo::dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(d_out, iters, 1.0 + rep);
+        OMO_CUDA(cudaEventRecord(e1, ctx->stream));
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        float ms = 0.f;
+        OMO_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = 2.0 * 64.0 * (double)iters * (double)blocks * threads;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out);
+    *flops_per_s = best;
+    return OMO_OK;
+}
+
+}  // extern "C"

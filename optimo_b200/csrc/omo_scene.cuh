@@ -1,0 +1,69 @@
+// Device-side scene tables and kernel parameter blocks of libomo (sm_100a).
+//
+// The joint tree is stored topology-sorted (DFS pre-order == RBDL body order, OptiMo/object.cpp:27-40,
+// OptiMo/core_rbdl.cpp:214-256) in CONSTANT memory so that every per-body quantity is a uniform operand of
+// the FP64 pipe. One scene is active per device at a time (omo.cu re-uploads the table when the active
+// context changes).
+#ifndef OMO_SCENE_CUH
+#define OMO_SCENE_CUH
+
+#include "../../include/omo.h"
+
+#define OMO_MAXJ OMO_MAX_JOINTS
+#define OMO_SLOT 12  // doubles per stack slot: (f, sincos) or (v, a) or (L, t)
+
+// Per-body constants: the RBDL quantities InverseDynamics reads (Model::X_T[i].r, Model::I[i];
+// external/rbdl-v2.5.0/src/Model.cc:258-464, include/rbdl/SpatialAlgebraOperators.h:116-128).
+struct OmoBody {
+    double r[3];                         // X_T.r == parent joint's offset (core_rbdl.cpp:228-252)
+    double m;                            // mass
+    double h[3];                         // m * com
+    double Ixx, Iyx, Iyy, Izx, Izy, Izz; // rotational inertia about the joint frame origin
+};
+
+struct OmoDevScene {
+    int J, n_ik;
+    int n_slots;  // stack slots per thread (each OMO_SLOT doubles)
+    int pad0;
+    int parent[OMO_MAXJ];
+    short fs_slot[OMO_MAXJ];  // slot of (f, sincos) while the body's subtree is open; -1 for leaves and the root
+    short va_slot[OMO_MAXJ];  // slot of (v, a) for non-root bodies with >= 2 children; -1 otherwise
+    short fk_slot[OMO_MAXJ];  // slot of the world affine (L, t) for bodies with >= 2 children; -1 otherwise
+    short ik_of[OMO_MAXJ];    // IK handler driving this joint's angles (joint.cpp:38-44), -1 if none
+    short ik_idx[OMO_MAXJ];   // position of the joint inside that handler's chain
+    short ik_start[OMO_MAXJ]; // IK handler whose chain root is this joint, -1 if none
+    unsigned char n_child[OMO_MAXJ];
+    unsigned char dyn[OMO_MAXJ];  // bit a: channel 3j+a is keyframed
+    // joint channels (3 per joint). pos = first position of the channel in the chain-ordered prepared arrays.
+    int chan_pos[3 * OMO_MAXJ];
+    int chan_n[3 * OMO_MAXJ];
+    double chan_const[3 * OMO_MAXJ];                      // Variable::var_
+    double chan_sin[3 * OMO_MAXJ], chan_cos[3 * OMO_MAXJ]; // of chan_const (host libm)
+    double chan_qd[3 * OMO_MAXJ], chan_qdd[3 * OMO_MAXJ];  // interior-stencil rounding residue of a constant (SURVEY §7 ix)
+    double root_qd[3], root_qdd[3];                        // same for q[0:3] = root offset (core_rbdl.cpp:137-141)
+    OmoBody body[OMO_MAXJ];
+    double offset[OMO_MAXJ][3];
+    // IK handlers (ikhandler.cpp:77-188)
+    int ik_nb[OMO_MAX_IK];                           // rotating joints in the chain
+    int ik_joint[OMO_MAX_IK][OMO_MAX_IK_CHAIN + 1];  // chain joints root..end effector
+    int ik_chan_pos[OMO_MAX_IK][3];
+    int ik_chan_n[OMO_MAX_IK][3];
+    double ik_chan_const[OMO_MAX_IK][3];
+};
+
+struct OmoEvalParams {
+    const double* prep;     // [B][6][n_cp] prepared control points, chain order (see prepare_kernel)
+    const unsigned* flags;  // [B] bit 0: every channel's chain is sorted by time
+    const double* tgrid;    // [N_s]
+    const double* wcost;    // [N_s] time-varying cost weight (core.cpp:191-199)
+    const double* p_orig;   // [3J][N_s] joint positions of the original motion
+    double* partial;        // [B][n_tiles][2]: (sum w*local_cost, sum w_traj*|p-p0|^2*dt)
+    int N_s, n_tiles, T_out, n_cp;
+    double dt, inv_dt, inv_2dt, inv_12dt, inv_dt2, inv_2dt2, inv_12dt2;
+    double w_traj;
+    // optional per-sample outputs of candidate 0 (OptimizationCache, core.h:120-152); sample-major
+    double *o_q, *o_qd, *o_qdd, *o_tau, *o_local, *o_p;
+    unsigned long long* counters;  // [4] or null
+};
+
+#endif

@@ -1,0 +1,430 @@
+// See core.hpp. Reference file:line cited per function (paths relative to /root/reference/).
+#include "core.hpp"
+
+#include <algorithm>
+#include <cassert>
+#include <cstdlib>
+#include <fstream>
+#include <iterator>
+
+#include "json.hpp"
+
+namespace optimo {
+
+namespace {
+
+constexpr double kPi = 3.14159265358979323846;
+
+// ---- scene JSON (OptiMo/core_io.cpp:100-151) ------------------------------------------------------------
+Variable InterpretJson2Variable(const Json& json)
+{
+    Variable var(json["var"].number_value());
+    for (const Json& j : json["curve"].array_items())
+        var.curve_.AddControlPoint(ControlPoint(j[0].number_value(), j[1].number_value(), j[2].number_value(), j[3].number_value(),
+                                                j[4].number_value()));
+    return var;
+}
+
+std::shared_ptr<Joint> InterpretJson2Joint(const Json& json, std::shared_ptr<Joint> parent = nullptr)
+{
+    const Vec3 offset{{json["offset"][0].number_value(), json["offset"][1].number_value(), json["offset"][2].number_value()}};
+    auto joint = std::make_shared<Joint>(parent, offset, InterpretJson2Variable(json["rot_x"]), InterpretJson2Variable(json["rot_y"]),
+                                         InterpretJson2Variable(json["rot_z"]), json["name"].string_value());
+    for (const Json& c : json["children"].array_items()) joint->AddChild(InterpretJson2Joint(c, joint));
+    return joint;
+}
+
+void InterpretJson2IkHandlerAndAddToObject(const Json& json, const std::shared_ptr<Object>& object)
+{
+    auto root = object->GetJointByName(json["root_name"].string_value());
+    auto end = object->GetJointByName(json["end_effector_name"].string_value());
+    if (!root || !end) throw std::runtime_error("IK handler refers to an unknown joint");
+    auto handler = std::make_shared<IkHandler>(json["name"].string_value());
+    handler->Initialize(root, end);
+    for (auto& j : handler->target_joints_)
+        if (j != end) j->associated_ik_handler_ = handler;
+    handler->pos_x_ = InterpretJson2Variable(json["pos_x"]);
+    handler->pos_y_ = InterpretJson2Variable(json["pos_y"]);
+    handler->pos_z_ = InterpretJson2Variable(json["pos_z"]);
+    object->AddIkHandler(handler);
+}
+
+Json Variable2Json(const Variable& var)
+{
+    Json curve = Json::array();
+    for (const ControlPoint& p : var.curve_.GetControlPoints()) {
+        Json cp = Json::array();
+        for (double v : {p.time, p.value, p.theta, p.time_backward, p.time_forward}) cp.push_back(Json::number(v));
+        curve.push_back(cp);
+    }
+    Json o = Json::object();
+    o.set("var", Json::number(var.var_));
+    o.set("curve", curve);
+    return o;
+}
+
+Json Joint2Json(const std::shared_ptr<Joint>& joint)
+{
+    Json children = Json::array();
+    for (const auto& c : joint->children_) children.push_back(Joint2Json(c));
+    Json off = Json::array();
+    for (double v : joint->offset_) off.push_back(Json::number(v));
+    Json o = Json::object();
+    o.set("name", Json::string(joint->name_));
+    o.set("offset", off);
+    o.set("rot_x", Variable2Json(joint->rot_x_));
+    o.set("rot_y", Variable2Json(joint->rot_y_));
+    o.set("rot_z", Variable2Json(joint->rot_z_));
+    o.set("children", children);
+    return o;
+}
+
+}  // namespace
+
+// ---- construction -------------------------------------------------------------------------------------------
+
+/// OptiMo/core.cpp:23-103 -- the default humanoid, default frozen dofs (t, v) and weights. Unlike the
+/// reference this constructor evaluates nothing: the engine is created on first use (never before main).
+Core::Core()
+{
+    object_ = std::make_shared<Object>();
+    auto V = [](double x, double y, double z) { return Vec3{{x, y, z}}; };
+    const Vec3 Z = V(0, 0, 0);
+    auto root = object_->GetRootJoint();
+    auto spine = root->AddChild(V(0.0, 0.2, 0.0), Z, "spine");
+    auto neck = spine->AddChild(V(0.0, 0.5, 0.0), Z, "neck");
+    neck->AddChild(V(0.0, 0.5, 0.0), Z, "head");
+    auto r_shld = spine->AddChild(V(-0.2, 0.5, 0.0), V(0.0, 0.0, +kPi / 6.0), "right_shoulder");
+    auto r_arm = r_shld->AddChild(V(-0.5, 0.0, 0.0), Z, "right_arm");
+    r_arm->AddChild(V(-0.5, 0.0, 0.0), Z, "right_hand");
+    auto l_shld = spine->AddChild(V(+0.2, 0.5, 0.0), V(0.0, 0.0, -kPi / 6.0), "left_shoulder");
+    auto l_arm = l_shld->AddChild(V(+0.5, 0.0, 0.0), V(0.0, -0.1 * kPi, 0.0), "left_arm");
+    l_arm->AddChild(V(+0.5, 0.0, 0.0), Z, "left_hand");
+    auto l_uleg = root->AddChild(V(+0.15, -0.10, 0.00), Z, "left_upleg");
+    auto l_leg = l_uleg->AddChild(V(0.03, -0.50, 0.05), Z, "left_leg");
+    auto l_foot = l_leg->AddChild(V(0.00, -0.50, -0.05), Z, "left_foot");
+    l_foot->AddChild(V(0.00, -0.05, 0.15), Z, "left_toe");
+    auto r_uleg = root->AddChild(V(-0.15, -0.10, 0.00), Z, "right_upleg");
+    auto r_leg = r_uleg->AddChild(V(-0.03, -0.50, 0.05), Z, "right_leg");
+    auto r_foot = r_leg->AddChild(V(0.00, -0.50, -0.05), Z, "right_foot");
+    r_foot->AddChild(V(0.00, -0.05, 0.15), Z, "right_toe");
+
+    struct Key { double t, v; };
+    auto keys = [](Variable& var, std::initializer_list<Key> ks) { for (const Key& k : ks) var.curve_.AddControlPoint(k.t, k.v); };
+    keys(spine->rot_z_, {{4, 0.0 * kPi}, {10, 0.1 * kPi}, {28, 0.1 * kPi}, {36, 0.0 * kPi}});
+    keys(r_shld->rot_z_, {{4, kPi / 4.0}, {10, kPi / 3.0}, {28, kPi / 3.0}, {36, kPi / 4.0}});
+    keys(l_arm->rot_z_, {{4, 0.0 * kPi}, {12, kPi / 6.0}, {20, kPi / 8.0}, {28, kPi / 6.0}, {36, 0.0 * kPi}});
+    keys(l_shld->rot_z_, {{4, -kPi / 4.0}, {12, 0.4 * kPi}, {20, 0.0 * kPi}, {26, 0.4 * kPi}, {36, -kPi / 4.0}});
+    keys(r_shld->rot_y_, {{4, 0.0 * kPi}, {10, -0.1 * kPi}, {28, -0.1 * kPi}, {36, 0.0 * kPi}});
+    keys(r_arm->rot_y_, {{4, 0.1 * kPi}, {10, 0.2 * kPi}, {28, 0.2 * kPi}, {36, 0.1 * kPi}});
+    root->offset_ = V(0.0, -0.6, 0.0);
+
+    const int n = static_cast<int>(object_->GetDescriptor().size()) / 5;
+    freezed_dofs_.assign(static_cast<size_t>(n) * 5, false);
+    for (int i = 0; i < n; ++i) { freezed_dofs_[i * 5 + 0] = true; freezed_dofs_[i * 5 + 1] = true; }
+    per_item_weights_.assign(object_->GetItems().size(), 0.0);
+    weight_trajectory_ = 0.0;
+    x_original_ = object_->GetDescriptor();
+
+    const char* dev = std::getenv("OPTIMO_DEVICE");
+    if (!dev) dev = std::getenv("LOCAL_RANK");
+    if (dev) device_ = std::atoi(dev);
+}
+
+Core::~Core()
+{
+    if (engine_) omo_destroy(engine_);
+}
+
+void Core::SetDevice(int device)
+{
+    if (device != device_) { device_ = device; InitializeDynamicsModel(); }
+}
+
+// ---- IO ---------------------------------------------------------------------------------------------------------
+
+void Core::ReadJson(const std::string& file_path)
+{
+    std::ifstream in(file_path);
+    if (!in) throw std::runtime_error("cannot open " + file_path);
+    ReadJsonString(std::string(std::istreambuf_iterator<char>(in), std::istreambuf_iterator<char>()));
+}
+
+/// core_io.cpp:228-250 (ApplyJsonToScene) + :154-163 (rebuild the dynamics model). The runtime state that the
+/// reference keeps only in UI-driven members (frozen dofs, weights, kernels, x_original) is
+/// reset to the Core() defaults for the new scene.
+void Core::ReadJsonString(const std::string& json_text)
+{
+    const Json json = Json::parse(json_text);
+    object_->SetRootJoint(nullptr);
+    object_->ClearIkHandlers();
+    min_frame_ = json["min_frame"].int_value();
+    max_frame_ = json["max_frame"].int_value();
+    frames_per_second_ = json["frames_per_second"].int_value();
+    if (json["joints"].type() != Json::Object) throw std::runtime_error("scene JSON has no \"joints\" object");
+    object_->SetRootJoint(InterpretJson2Joint(json["joints"]));
+    for (const Json& h : json["ik_handlers"].array_items()) InterpretJson2IkHandlerAndAddToObject(h, object_);
+    ClearOptimizationCache();
+
+    const int n = static_cast<int>(object_->GetDescriptor().size()) / 5;
+    freezed_dofs_.assign(static_cast<size_t>(n) * 5, false);
+    for (int i = 0; i < n; ++i) { freezed_dofs_[i * 5 + 0] = true; freezed_dofs_[i * 5 + 1] = true; }
+    per_item_weights_.assign(object_->GetItems().size(), 0.0);
+    weight_trajectory_ = 0.0;
+    kernels_.clear();
+    x_original_ = object_->GetDescriptor();
+    InitializeDynamicsModel();
+}
+
+std::string Core::ConvertCurrentSceneToJson() const
+{
+    Json iks = Json::array();
+    for (const auto& h : object_->GetIkHandlers()) {
+        Json o = Json::object();
+        o.set("name", Json::string(h->name_));
+        o.set("pos_x", Variable2Json(h->pos_x_));
+        o.set("pos_y", Variable2Json(h->pos_y_));
+        o.set("pos_z", Variable2Json(h->pos_z_));
+        o.set("root_name", Json::string(h->ik_root_->name_));
+        o.set("end_effector_name", Json::string(h->end_effector_->name_));
+        iks.push_back(o);
+    }
+    Json obj = Json::object();
+    obj.set("min_frame", Json::number(min_frame_));
+    obj.set("max_frame", Json::number(max_frame_));
+    obj.set("frames_per_second", Json::number(frames_per_second_));
+    obj.set("joints", Joint2Json(object_->GetRootJoint()));
+    obj.set("ik_handlers", iks);
+    return obj.dump();
+}
+
+void Core::WriteJson(const std::string& file_path) const
+{
+    std::ofstream out(file_path);
+    out << ConvertCurrentSceneToJson();
+}
+
+// ---- weights / frozen dofs ------------------------------------------------------------------------------------------
+
+void Core::UpdateFreezedDofsFromSelection()
+{
+    const int n = static_cast<int>(object_->GetDescriptor().size()) / 5;
+    freezed_dofs_.assign(static_cast<size_t>(n) * 5, true);
+    int cp = 0;
+    for (const auto& item : object_->GetItems()) {
+        const int begin = cp;
+        for (Variable* v : item->GetVariablePointers()) cp += v->GetNumOfControlPoints();
+        if (!item->is_selected_) continue;
+        for (int i = begin; i < cp; ++i) { freezed_dofs_[i * 5 + 2] = false; freezed_dofs_[i * 5 + 3] = false; freezed_dofs_[i * 5 + 4] = false; }
+    }
+}
+
+void Core::UpdateGlobalWeight(double weight) { weight_trajectory_ = weight; }
+
+void Core::UpdatePerItemWeight(double weight, const std::string& item_name)
+{
+    const int index = object_->GetItemIndexByName(item_name);
+    if (index < 0) throw std::invalid_argument("no item named " + item_name);
+    per_item_weights_[index] = weight;
+}
+
+VecN Core::CalculateParameterWeights() const
+{
+    const int n = static_cast<int>(object_->GetDescriptor().size()) / 5;
+    VecN w(static_cast<size_t>(n) * 5, weight_trajectory_);
+    int item_index = 0, cp = 0;
+    for (const auto& item : object_->GetItems()) {
+        for (Variable* v : item->GetVariablePointers()) {
+            const int np = v->GetNumOfControlPoints();
+            for (int k = cp * 5; k < (cp + np) * 5; ++k) w[k] += per_item_weights_[item_index];
+            cp += np;
+        }
+        ++item_index;
+    }
+    return w;
+}
+
+void Core::UpdateOriginalParameters(const VecN& x_original) { x_original_ = x_original; }
+
+double Core::GetCostWeight(double t) const
+{
+    double w = 1.0;
+    for (const GaussianKernel& k : kernels_) w -= k.GetValue(t);
+    return std::max(w, 0.0);
+}
+
+// ---- engine ---------------------------------------------------------------------------------------------------------------
+
+void Core::Check(omo_status st, const char* what)
+{
+    if (st == OMO_OK) return;
+    throw engine_error(std::string(what) + ": " + omo_last_error(engine_));
+}
+
+void Core::InitializeDynamicsModel()
+{
+    if (engine_) { omo_destroy(engine_); engine_ = nullptr; }
+    ClearOptimizationCache();
+    have_last_ = false;
+}
+
+/// Flattens the object graph into the tables of omo_scene_desc: what Core::InitializeDynamicsModel
+/// (core_rbdl.cpp:200-262) feeds to RBDL plus the channel / control-point layout of Object::GetDescriptor.
+omo_ctx* Core::Engine()
+{
+    if (engine_) return engine_;
+    const auto joints = object_->GetJoints();
+    const auto iks = object_->GetIkHandlers();
+    const int J = static_cast<int>(joints.size());
+    std::vector<int> parent(J, -1), ik_root, ik_end, first_cp, n_cp_ch, chain;
+    std::vector<double> offset(3 * J), mass(J), com(3 * J), inertia(9 * J), chan_const;
+    auto index_of = [&](const std::shared_ptr<Joint>& j) { return static_cast<int>(std::find(joints.begin(), joints.end(), j) - joints.begin()); };
+    for (int k = 0; k < J; ++k) {
+        const auto& j = joints[k];
+        if (auto p = j->parent_.lock()) parent[k] = index_of(p);
+        for (int a = 0; a < 3; ++a) { offset[3 * k + a] = j->offset_[a]; com[3 * k + a] = j->center_of_mass_position_parent_[a]; }
+        mass[k] = j->mass_;
+        for (int a = 0; a < 9; ++a) inertia[9 * k + a] = j->inertia_at_center_parent_[a];
+    }
+    int cp_total = 0;
+    auto add_channel = [&](const Variable& v) {
+        chan_const.push_back(v.var_);
+        const int n = v.GetNumOfControlPoints();
+        first_cp.push_back(n > 0 ? cp_total : -1);
+        n_cp_ch.push_back(n);
+        for (int idx : v.curve_.ChainOrder()) chain.push_back(cp_total + idx);
+        cp_total += n;
+    };
+    for (const auto& j : joints) { add_channel(j->rot_x_); add_channel(j->rot_y_); add_channel(j->rot_z_); }
+    for (const auto& h : iks) {
+        add_channel(h->pos_x_); add_channel(h->pos_y_); add_channel(h->pos_z_);
+        ik_root.push_back(index_of(h->ik_root_));
+        ik_end.push_back(index_of(h->end_effector_));
+    }
+    omo_scene_desc d;
+    d.n_joints = J; d.parent = parent.data(); d.offset = offset.data(); d.mass = mass.data(); d.com = com.data(); d.inertia = inertia.data();
+    d.n_ik = static_cast<int>(iks.size()); d.ik_root = ik_root.data(); d.ik_end = ik_end.data();
+    d.n_channels = static_cast<int>(chan_const.size()); d.chan_const = chan_const.data(); d.chan_first_cp = first_cp.data();
+    d.chan_n_cp = n_cp_ch.data(); d.n_cp = cp_total; d.chain = chain.data();
+    const omo_status st = omo_create(&d, device_, &engine_);
+    if (st != OMO_OK) { engine_ = nullptr; throw engine_error(std::string("omo_create: ") + omo_last_error(nullptr)); }
+    return engine_;
+}
+
+/// Snapshots the state the objective reads (weights, kernels, cyclic flag, window, x_original) into the engine.
+/// Called at the top of every evaluation so that mid-solve slider changes behave as in the reference.
+void Core::SyncEngine(double min_t, double max_t, const VecN& x_original)
+{
+    omo_ctx* e = Engine();
+    const VecN w = CalculateParameterWeights();
+    if (x_original.size() != w.size()) throw std::invalid_argument("x_original has the wrong length");
+    Check(omo_set_window(e, min_t, max_t, 0.20), "omo_set_window");   // dt = 0.20, core_rbdl.cpp:351
+    std::vector<omo_gauss> ks;
+    for (const GaussianKernel& k : kernels_) ks.push_back(omo_gauss{k.amp, k.mu, k.sigma});
+    Check(omo_set_weights(e, w.data(), static_cast<int>(w.size()), weight_trajectory_, ks.data(), static_cast<int>(ks.size()),
+                          object_->is_cyclic_ ? 1 : 0), "omo_set_weights");
+    Check(omo_set_original(e, x_original.data(), static_cast<int>(x_original.size())), "omo_set_original");
+}
+
+double Core::CalculateFullObjective(double min_t, double max_t, const VecN& x, const VecN& x_original)
+{
+    SyncEngine(min_t, max_t, x_original);
+    if (x.size() != x_original.size()) throw std::invalid_argument("x has the wrong length");
+    double f = 0.0;
+    Check(omo_eval(engine_, x.data(), 1, &f, &last_terms_), "omo_eval");
+    object_->SetDescriptor(x);  // the reference leaves the object at x (core_rbdl.cpp:371)
+    {
+        std::lock_guard<std::mutex> g(optimization_cache_mutex_);
+        last_x_ = x; last_min_t_ = min_t; last_max_t_ = max_t; have_last_ = true; cache_stale_ = true;
+    }
+    return f;
+}
+
+void Core::CalculateFullObjectiveBatch(double min_t, double max_t, const double* X, int B, const VecN& x_original, double* f_out,
+                                       omo_terms* terms_out)
+{
+    SyncEngine(min_t, max_t, x_original);
+    Check(omo_eval(engine_, X, B, f_out, terms_out), "omo_eval");
+}
+
+double Core::CalculateFullObjectiveAndGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
+                                               const std::vector<int>& free_indices, double h, VecN* grad, VecN* f_plus_minus)
+{
+    SyncEngine(min_t, max_t, x_original);
+    if (x.size() != x_original.size()) throw std::invalid_argument("x has the wrong length");
+    const int F = static_cast<int>(free_indices.size());
+    grad->assign(F, 0.0);
+    if (f_plus_minus) f_plus_minus->assign(2 * static_cast<size_t>(F), 0.0);
+    double f0 = 0.0;
+    Check(omo_eval_grad(engine_, x.data(), free_indices.data(), F, h, &f0, grad->data(), f_plus_minus ? f_plus_minus->data() : nullptr),
+          "omo_eval_grad");
+    return f0;
+}
+
+std::vector<double> Core::CalculatePositions(double min_t, double max_t, const VecN& x)
+{
+    SyncEngine(min_t, max_t, x_original_);
+    std::vector<double> p(static_cast<size_t>(omo_num_samples(engine_)) * omo_dof(engine_));
+    Check(omo_positions(engine_, x.data(), p.data()), "omo_positions");
+    return p;
+}
+
+Core::OptimizationCache Core::GetOptimizationCache()
+{
+    std::lock_guard<std::mutex> g(optimization_cache_mutex_);
+    if (cache_stale_ || optimization_cache_.time_sequence.empty()) {
+        // The reference computes CalculateCost(min_frame-1, max_frame+1, 0.2) of the current object when no cache
+        // exists (core.h:136-139); otherwise the cache belongs to the last evaluated x.
+        VecN x = have_last_ ? last_x_ : object_->GetDescriptor();
+        const double lo = have_last_ ? last_min_t_ : min_frame_ - 1.0, hi = have_last_ ? last_max_t_ : max_frame_ + 1.0;
+        SyncEngine(lo, hi, x_original_.size() == x.size() ? x_original_ : x);
+        const int n = omo_num_samples(engine_), dof = omo_dof(engine_);
+        std::vector<double> q((size_t)n * dof), qd((size_t)n * dof), qdd((size_t)n * dof), tau((size_t)n * dof), lc(n), ts(n);
+        Check(omo_eval_cached(engine_, x.data(), nullptr, nullptr, q.data(), qd.data(), qdd.data(), tau.data(), lc.data()), "omo_eval_cached");
+        Check(omo_get_time_grid(engine_, ts.data()), "omo_get_time_grid");
+        OptimizationCache c;
+        c.time_sequence = ts; c.local_cost_sequence = lc;
+        auto rows = [&](const std::vector<double>& a) {
+            std::vector<VecN> out(n);
+            for (int i = 0; i < n; ++i) out[i].assign(a.begin() + (size_t)i * dof, a.begin() + (size_t)(i + 1) * dof);
+            return out;
+        };
+        c.q = rows(q); c.q_dot = rows(qd); c.q_ddot = rows(qdd); c.tau = rows(tau);
+        optimization_cache_ = c;
+        cache_stale_ = false;
+    }
+    return optimization_cache_;
+}
+
+void Core::ClearOptimizationCache()
+{
+    std::lock_guard<std::mutex> g(optimization_cache_mutex_);
+    optimization_cache_ = OptimizationCache();
+    cache_stale_ = true;
+}
+
+// ---- the NLopt callback (core_opt.cpp:42-57) ------------------------------------------------------------------------------------
+
+double EvaluateObjective(const std::vector<double>& x, std::vector<double>& grad, void* data)
+{
+    EvaluateObjectiveData* d = static_cast<EvaluateObjectiveData*>(data);
+    Core& core = *d->core;
+    // revert: X^T x + Y x_initial
+    VecN full = d->x_initial;
+    if (x.size() != d->free_indices.size()) throw std::invalid_argument("EvaluateObjective: wrong number of free dofs");
+    for (size_t k = 0; k < x.size(); ++k) full[d->free_indices[k]] = x[k];
+    if (core.stop_optimization_) {
+        core.stop_optimization_ = false;
+        throw forced_stop();
+    }
+    d->evaluations += 1;
+    if (d->want_gradient && !grad.empty()) {
+        VecN g;
+        const double f = core.CalculateFullObjectiveAndGradient(d->min_t, d->max_t, full, d->x_original, d->free_indices, d->gradient_step, &g);
+        std::copy(g.begin(), g.end(), grad.begin());
+        return f;
+    }
+    return core.CalculateFullObjective(d->min_t, d->max_t, full, d->x_original);
+}
+
+}  // namespace optimo

@@ -1,0 +1,144 @@
+// Headless `Core` of the B200 OptiMo objective path: same public names, argument meaning and error
+// behaviour as the reference's Core for everything the objective path touches (OptiMo/core.h:35-245),
+// minus camera / drawing / Qt. The arithmetic is NOT here: CalculateFullObjective and friends forward to the
+// CUDA engine behind include/omo.h (libomo.so). There is no CPU implementation of the objective in this class.
+//
+// The Eigen::VectorXd arguments of the reference become std::vector<double> (Eigen is not a dependency).
+#ifndef OPTIMO_B200_CORE_HPP
+#define OPTIMO_B200_CORE_HPP
+
+#include <cmath>
+#include <list>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/omo.h"
+#include "object.hpp"
+
+namespace optimo {
+
+/// Gaussian kernel: amp * exp(- (x - mu)^2 / (2 sigma^2))   (OptiMo/core.h:27-33)
+struct GaussianKernel {
+    double amp, mu, sigma;
+    double GetValue(double x) const { return amp * std::exp(-(x - mu) * (x - mu) / (2.0 * sigma * sigma)); }
+};
+
+/// Thrown (like nlopt::forced_stop) by EvaluateObjective when Core::stop_optimization_ is set (core_opt.cpp:50-54).
+struct forced_stop : std::runtime_error { forced_stop() : std::runtime_error("nlopt forced stop") {} };
+/// Any failure of the CUDA engine (there is no fallback path).
+struct engine_error : std::runtime_error { explicit engine_error(const std::string& m) : std::runtime_error(m) {} };
+
+class Core {
+public:
+    Core();   // default humanoid (core.cpp:23-103); touches no CUDA state
+    ~Core();
+    Core(const Core&) = delete;
+    Core& operator=(const Core&) = delete;
+
+    static Core& GetInstance() { static Core core; return core; }
+
+    int min_frame_ = 1, max_frame_ = 40, current_frame_ = 1, frames_per_second_ = 24;
+    /// If true, the next objective callback throws forced_stop (set from another thread; core.h:64-66).
+    bool stop_optimization_ = false;
+    std::shared_ptr<Object> object_;
+
+    /// True: the dof is not optimised. Same order as the descriptor (core.h:73-76).
+    std::vector<bool> freezed_dofs_;
+    void UpdateFreezedDofsFromSelection();                                  // core.cpp:118-148
+    std::vector<double> per_item_weights_;
+    void UpdatePerItemWeight(double weight, const std::string& item_name);  // core.cpp:155-159
+    double weight_trajectory_ = 0.0;
+    void UpdateGlobalWeight(double weight);                                 // core.cpp:150-153
+
+    /// core_opt.cpp:60-157 -- LN_BOBYQA over the free dofs through NLopt (loaded at run time, see core_opt.cpp).
+    void PerformOptimization(bool explicit_termination = false);
+
+    /// core_rbdl.cpp:348-401. Like the reference it leaves the object at `x`.
+    double CalculateFullObjective(double min_t, double max_t, const VecN& x, const VecN& x_original);
+    /// Batch form: X is row-major [B][D] in host memory; f_out[B]; terms_out[B] optional.
+    void CalculateFullObjectiveBatch(double min_t, double max_t, const double* X, int B, const VecN& x_original, double* f_out,
+                                     omo_terms* terms_out = nullptr);
+    /// NEW: f(x) and its central-difference gradient on the free dofs.
+    double CalculateFullObjectiveAndGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
+                                             const std::vector<int>& free_indices, double h, VecN* grad, VecN* f_plus_minus = nullptr);
+    /// (C, D_param, D_traj) of the last CalculateFullObjective call.
+    omo_terms last_terms_{0, 0, 0};
+
+    void ReadJson(const std::string& file_path);          // core_io.cpp:154-163
+    void ReadJsonString(const std::string& json_text);    // ApplyJsonToScene + InitializeDynamicsModel
+    void WriteJson(const std::string& file_path) const;   // core_io.cpp:165-169
+    std::string ConvertCurrentSceneToJson() const;        // core_io.cpp:216-226
+
+    struct OptimizationCache {  // core.h:120-131
+        std::vector<double> time_sequence;
+        std::vector<VecN> q, q_dot, q_ddot, tau;
+        std::vector<double> local_cost_sequence;
+        int GetSize() const { return static_cast<int>(time_sequence.size()); }
+    };
+    /// Thread-safe copy. The per-sample arrays of the last evaluated x are fetched from the GPU on demand
+    /// (the reference fills them on every evaluation, core_rbdl.cpp:341-343; the observable content is the same).
+    OptimizationCache GetOptimizationCache();
+    void ClearOptimizationCache();
+
+    void UpdateOriginalParameters(const VecN& x_original);                       // core.cpp:184-189
+    const VecN& RetrieveOriginalParameters() const { return x_original_; }
+    void AddKernel(double t) { kernels_.push_back(GaussianKernel{1.0, t, 1.0}); }  // core.h:163
+    double GetCostWeight(double t) const;                                          // core.cpp:191-199
+    GaussianKernel* GetKernelPointer(int index) { return &kernels_[index]; }
+    GaussianKernel* GetLastKernelPointer() { return GetKernelPointer(static_cast<int>(kernels_.size()) - 1); }
+    void ClearKernels() { kernels_.clear(); }
+    int GetNumKernels() const { return static_cast<int>(kernels_.size()); }
+
+    VecN CalculateParameterWeights() const;   // core.cpp:161-182
+    /// Joint world positions (N_s x 3J) of descriptor x over [min_t, max_t] (SetStates' p, core_rbdl.cpp:150-153).
+    std::vector<double> CalculatePositions(double min_t, double max_t, const VecN& x);
+
+    /// CUDA device the engine is created on (default 0, or $OPTIMO_DEVICE / $LOCAL_RANK).
+    void SetDevice(int device);
+    int GetDevice() const { return device_; }
+    /// The engine behind the objective; created lazily (never before main), rebuilt when the scene changes.
+    omo_ctx* Engine();
+    /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
+    void InitializeDynamicsModel();
+
+    /// Result of the last PerformOptimization (function value, evaluations).
+    double last_solve_value_ = 0.0;
+    int last_solve_evals_ = 0;
+    std::string last_solve_status_;
+
+private:
+    void SyncEngine(double min_t, double max_t, const VecN& x_original);
+    void Check(omo_status st, const char* what);
+
+    std::vector<GaussianKernel> kernels_;
+    VecN x_original_;
+    omo_ctx* engine_ = nullptr;
+    int device_ = 0;
+
+    std::mutex optimization_cache_mutex_;
+    OptimizationCache optimization_cache_;
+    bool cache_stale_ = true;
+    VecN last_x_;
+    double last_min_t_ = 0.0, last_max_t_ = 0.0;
+    bool have_last_ = false;
+};
+
+/// nlopt::vfunc-compatible objective (core_opt.cpp:42-57): `data` is an EvaluateObjectiveData*.
+/// `grad` is filled only when data->want_gradient is set AND grad is non-empty (SURVEY.md §8(b) trap).
+struct EvaluateObjectiveData {
+    Core* core;
+    double min_t, max_t;
+    VecN x_original;   // #{full dofs}
+    VecN x_initial;    // #{full dofs}: values of the frozen dofs (Y * x_initial, core_opt.cpp:121)
+    std::vector<int> free_indices;  // X: free -> full
+    bool want_gradient = false;
+    double gradient_step = 1e-4;
+    int evaluations = 0;
+};
+double EvaluateObjective(const std::vector<double>& x, std::vector<double>& grad, void* data);
+
+}  // namespace optimo
+#endif

@@ -1,0 +1,143 @@
+"""CPU-side checks of the product: the C-ABI libraries load and export every symbol the headers declare,
+the host mirror of the reference's Core/Object (JSON, descriptor, physical parameters, weights, frozen
+dofs) agrees with the oracle, and the compute path fails LOUDLY without a GPU (no CPU fallback)."""
+import ctypes
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, SCENES, load_scene, scene_path
+
+import optimo_b200
+from optimo_b200 import synthetic
+from optimo_b200.core import Core, EngineError, grad_from_columns, shard_range
+
+
+def _declared(header):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b((?:omo|optimo)_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.mark.parametrize("header,lib", [("omo.h", "omo"), ("optimo_core.h", "core")])
+def test_library_exports_every_declared_symbol(header, lib):
+    names = _declared(header)
+    assert len(names) > 20
+    handle = ctypes.CDLL(optimo_b200.lib_paths()[lib])
+    missing = [n for n in names if not hasattr(handle, n)]
+    assert not missing, missing
+
+
+def test_no_oracle_dependency_in_product():
+    """The product must never import, link or call oracle/ (checked on sources and on the linked libraries)."""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "optimo_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cpp", ".hpp", ".cu", ".cuh", ".h", "Makefile")):
+                text = open(os.path.join(dirpath, fn), errors="ignore").read()
+                assert "liboracle" not in text and "oracle/" not in text and "import oracle" not in text, os.path.join(dirpath, fn)
+    for p in optimo_b200.lib_paths().values():
+        assert b"liboracle" not in open(p, "rb").read()
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_scene_json_flattening_matches_oracle(oracle_port, name):
+    o = oracle_port.Oracle(load_scene(name), "port")
+    c = Core(scene_path(name))
+    assert c.J == o.J and c.D == o.D
+    assert c.item_names() == o.item_names
+    assert np.array_equal(c.GetDescriptor(), o.descriptor())
+    assert np.array_equal(c.freezed_dofs_, o.freezed())
+    for j in range(c.J):
+        m, com, I = c.joint_physical(j)
+        mo, como, Io = o.joint_physical(j)
+        assert m == mo and np.array_equal(com, como)
+        assert np.allclose(I, Io, rtol=1e-13, atol=1e-17)
+    # descriptor round trip and cyclic tangent averaging (object.cpp:147-186)
+    x = c.GetDescriptor() + 0.01
+    c.SetDescriptor(x)
+    assert np.array_equal(c.GetDescriptor(), x)
+    c.set_cyclic(True); o.set_cyclic(True)
+    c.SetDescriptor(x); o.lib.orc_set_descriptor(o.h, x.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), x.size)
+    assert np.array_equal(c.GetDescriptor(), o.descriptor())
+
+
+def test_weights_selection_and_kernels_match_oracle(oracle_port):
+    o = oracle_port.Oracle(load_scene("conductor"), "port")
+    c = Core(scene_path("conductor"))
+    for obj, setter in ((o, lambda n, w: o.set_per_item_weight(n, w)), (c, lambda n, w: c.UpdatePerItemWeight(w, n))):
+        setter("Spine", 2.5); setter("LeftArmIK", 0.75)
+    o.set_weight_trajectory(12.5); c.UpdateGlobalWeight(12.5)
+    assert np.array_equal(c.CalculateParameterWeights(), o.parameter_weights())
+    o.select_items(["Spine", "LeftArmIK"]); c.select_items(["Spine", "LeftArmIK"])
+    assert np.array_equal(c.freezed_dofs_, o.freezed())
+    ks = [(1.0, 20.0, 2.6), (1.0, 10.0, 1.0)]
+    o.set_kernels(ks); c.set_kernels(ks)
+    for t in (-2.0, 9.3, 10.0, 19.0, 21.7, 42.0):
+        assert c.GetCostWeight(t) == o.cost_weight(t)
+    with pytest.raises(EngineError):
+        c.UpdatePerItemWeight(1.0, "no-such-item")
+
+
+def test_default_humanoid_is_the_stick_figure_scene():
+    """Core::Core() (core.cpp:23-103) builds the humanoid that scene-stick-figure.json stores."""
+    a, b = Core(), Core(scene_path("stick-figure"))
+    assert a.item_names() == b.item_names()
+    assert np.allclose(a.GetDescriptor(), b.GetDescriptor(), rtol=0, atol=1e-15)
+
+
+def test_json_write_read_round_trip(tmp_path):
+    c = Core(scene_path("conductor"))
+    p = tmp_path / "scene.json"
+    c.WriteJson(p)
+    d = Core(p)
+    assert d.item_names() == c.item_names() and np.array_equal(d.GetDescriptor(), c.GetDescriptor())
+    assert json.loads(c.scene_json())["ik_handlers"][0]["root_name"] == "LeftArm"
+    with pytest.raises(EngineError):
+        Core().ReadJsonString("{ not json")
+
+
+def test_shard_range_and_gradient_assembly():
+    for n, world in ((937, 8), (157, 4), (5, 8), (0, 2), (64, 1)):
+        spans = [shard_range(n, r, world) for r in range(world)]
+        assert spans[0][0] == 0 and sum(c for _, c in spans) == n
+        for (b0, c0), (b1, _) in zip(spans, spans[1:]):
+            assert b1 == b0 + c0
+        assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
+    cols = np.array([5.0, 7.0, 3.0, 2.0, 2.5])
+    f0, g = grad_from_columns(cols, 0.25)
+    assert f0 == 5.0 and np.array_equal(g, [(7.0 - 3.0) / 0.5, (2.0 - 2.5) / 0.5])
+
+
+def test_synthetic_generators():
+    rng = synthetic.MT19937_64([5489])
+    assert int(rng.next_u64()[0]) == 14514284786278117030   # std::mt19937_64 default-seed first output
+    assert int(rng.next_u64()[0]) == 4620546740167642908
+    stick = load_scene("stick-figure")
+    big = synthetic.stick_240(stick)
+    assert synthetic.count_control_points(big) == 156 and big["max_frame"] == 240
+    c = Core(big)
+    assert c.D == 780 and c.free_indices().size == 468
+    X = synthetic.perturbed_candidates(c.GetDescriptor(), 5)
+    assert X.shape == (5, 780) and np.array_equal(X[:, 0::5], np.tile(c.GetDescriptor()[0::5], (5, 1)))
+    assert (X[:, 3::5] <= -0.5).all() and (X[:, 4::5] >= 0.5).all()
+    assert np.array_equal(X[3], synthetic.perturbed_candidates(c.GetDescriptor(), 1, first=3)[0])
+    tree = synthetic.tree_scene()
+    assert synthetic.count_control_points(tree) == 37989
+    assert Core(tree).J == 64
+
+
+def test_compute_fails_loudly_without_a_gpu():
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if has_gpu:
+        pytest.skip("a GPU is present; the loud-failure path is for CPU-only hosts")
+    c = Core(scene_path("stick-figure"))
+    x = c.GetDescriptor()
+    with pytest.raises(EngineError, match="no usable CUDA device"):
+        c.CalculateFullObjective(-1.0, 42.0, x, x)

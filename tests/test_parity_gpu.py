@@ -1,0 +1,219 @@
+"""Parity of the CUDA path (through the C ABI / headless Core) against the CPU oracle and the committed goldens.
+
+Bar (BASELINE.json north_star): objective and gradient values within 1e-9 relative in FP64. The per-stage
+arrays (q, qd, qdd, tau, local_cost, positions) are compared much tighter -- they only differ by FMA
+contraction and libm-vs-libdevice last-ulp effects.
+"""
+import numpy as np
+import pytest
+
+from conftest import SCENES, all_cases, configure, load_cases, load_scene, rel_err, scene_path
+
+from optimo_b200 import synthetic
+from optimo_b200.core import Core, EngineError, ForcedStop, grad_from_columns, shard_range
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-9       # the contract
+TIGHT = 2e-11    # what the kernels actually achieve on smooth stages
+
+
+def _product_for(name, case):
+    c = Core(scene_path(name))
+    configure(c, case, False)
+    return c
+
+
+@pytest.mark.parametrize("name,tag", all_cases())
+def test_objective_terms_and_cache_match_goldens(name, tag):
+    cases, g = load_cases(name)
+    case = next(k for k in cases if k["tag"] == tag)
+    c = _product_for(name, case)
+    x, x0 = g[f"{tag}/x"], g[f"{tag}/x_original"]
+    c.UpdateOriginalParameters(x0)
+    lo, hi = c.window
+    f, terms = c.CalculateFullObjective(lo, hi, x, x0, want_terms=True)
+    fg = float(g[f"{tag}/f"])
+    assert abs(f - fg) <= TOL * abs(fg), (f, fg)
+    assert np.allclose(terms, g[f"{tag}/terms"], rtol=TOL, atol=1e-12)
+    cache = c.GetOptimizationCache()
+    assert np.array_equal(cache["time"], g[f"{tag}/time"])          # the accumulated t += 0.2 grid, bit for bit
+    for k in ("q", "qd", "qdd", "tau", "local_cost"):
+        assert cache[k].shape == g[f"{tag}/{k}"].shape, k
+        tol = TIGHT if "ik" not in tag else 1e-9                       # IK angles are themselves converged to 1e-6 only
+        assert rel_err(cache[k], g[f"{tag}/{k}"]) <= tol, (k, rel_err(cache[k], g[f"{tag}/{k}"]))
+    assert rel_err(c.positions(lo, hi, x), g[f"{tag}/positions"]) <= (TIGHT if "ik" not in tag else 1e-9)
+    # the reference leaves the object at x (core_rbdl.cpp:371)
+    xx = c.GetDescriptor()
+    if not case["cyclic"]:
+        assert np.array_equal(xx, x)
+
+
+@pytest.mark.parametrize("name,tag", all_cases())
+def test_finite_difference_gradient_matches_goldens(name, tag):
+    cases, g = load_cases(name)
+    case = next(k for k in cases if k["tag"] == tag)
+    c = _product_for(name, case)
+    x, x0 = g[f"{tag}/x"], g[f"{tag}/x_original"]
+    c.UpdateOriginalParameters(x0)
+    lo, hi = c.window
+    assert np.array_equal(c.free_indices(), g[f"{tag}/free_idx"])
+    f0, grad, fpm = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
+    assert abs(f0 - float(g[f"{tag}/f0"])) <= TOL * abs(float(g[f"{tag}/f0"]))
+    assert np.max(np.abs(fpm - g[f"{tag}/fpm"]) / np.abs(g[f"{tag}/fpm"])) <= TOL       # every perturbed value
+    gg = g[f"{tag}/grad"]
+    # the quotient amplifies value noise by 1/(2h); compare at 1e-9 * max(|g|_inf, 1) ... plus that noise
+    noise = 4e-13 * abs(f0) / 2e-4
+    assert np.max(np.abs(grad - gg)) <= TOL * max(np.max(np.abs(gg)), 1.0) + noise
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_batch_matches_oracle_on_seeded_candidates(oracle_port, name):
+    scene = load_scene(name)
+    o = oracle_port.Oracle(scene, "port")
+    o.set_sampling_concurrency(1)
+    c = Core(scene_path(name))
+    o.set_weight_trajectory(5.0); c.UpdateGlobalWeight(5.0)
+    x0 = c.GetDescriptor()
+    B = 24
+    X = synthetic.perturbed_candidates(x0, B, seed_base=0xB200)
+    lo, hi = c.window
+    f, terms = c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True)
+    for b in range(B):
+        fo, to = o.full_objective(X[b], x0)
+        assert abs(f[b] - fo) <= TOL * abs(fo), (b, f[b], fo)
+        assert np.allclose(terms[b], to, rtol=TOL, atol=1e-12)
+    # single-candidate API == row of the batch, bit for bit (same kernels, same reduction order)
+    assert c.CalculateFullObjective(lo, hi, X[5], x0) == f[5]
+
+
+def test_evaluate_objective_callback_and_cancel():
+    """EvaluateObjective (core_opt.cpp:42-57): free -> full expansion, forced_stop on the cancel flag."""
+    c = Core(scene_path("stick-figure"))
+    x0 = c.GetDescriptor()
+    idx = c.free_indices()
+    assert idx.size == 78
+    rng = np.random.default_rng(5)
+    xf = x0[idx] + 0.01 * rng.standard_normal(idx.size)
+    full = x0.copy(); full[idx] = xf
+    lo, hi = c.window
+    f = c.EvaluateObjective(xf, x0)
+    assert f == c.CalculateFullObjective(lo, hi, full, x0)
+    f2, g = c.EvaluateObjective(xf, x0, want_gradient=True)
+    assert f2 == f
+    _, g_ref, _ = c.CalculateGradient(lo, hi, full, x0)
+    assert np.array_equal(g, g_ref)
+    c.stop_optimization_ = True
+    with pytest.raises(ForcedStop):
+        c.EvaluateObjective(xf, x0)
+    assert c.stop_optimization_ is False        # the flag is consumed (core_opt.cpp:52)
+    assert c.EvaluateObjective(xf, x0) == f
+
+
+def test_unsorted_chain_and_out_of_range_samples(oracle_port):
+    """Control-point times are parameters: when a candidate moves a key past its neighbour the reference's
+    first-match-in-list-order segment search decides (curve.cpp:100-128)."""
+    scene = load_scene("stick-figure")
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1)
+    c = Core(scene_path("stick-figure"))
+    x0 = c.GetDescriptor()
+    x = x0.copy()
+    x[0] = 11.5        # first key of the first keyed channel jumps over the second one (t = 10)
+    x[5 * 7] = 2.0     # another channel: a key moved before the first one
+    lo, hi = c.window
+    f = c.CalculateFullObjective(lo, hi, x, x0)
+    fo, _ = o.full_objective(x, x0)
+    assert abs(f - fo) <= TOL * abs(fo)
+    # a window far outside every key: all curves clamp to their end values -> zero torque, zero cost
+    f_far = c.CalculateFullObjective(100.0, 120.0, x0, x0)
+    fo_far, _ = o.full_objective(x0, x0, window=(100.0, 120.0))
+    assert abs(f_far - fo_far) <= 1e-12 and abs(f_far) < 1e-20
+
+
+def test_small_windows_and_boundary_stencils(oracle_port):
+    """N_s = 3, 4, 5, 6 exercise every branch of the one-sided / 3-point / 5-point stencils (core_rbdl.cpp:28-95)."""
+    scene = load_scene("fox-tail")
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1)
+    c = Core(scene_path("fox-tail"))
+    x0 = c.GetDescriptor()
+    for hi in (10.45, 10.65, 10.85, 11.05, 35.0):
+        f = c.CalculateFullObjective(10.0, hi, x0, x0)
+        fo, _ = o.full_objective(x0, x0, window=(10.0, hi))
+        assert abs(f - fo) <= TOL * abs(fo) + 1e-15, (hi, f, fo)
+    with pytest.raises(EngineError):
+        c.CalculateFullObjective(10.0, 10.3, x0, x0)      # 2 samples: the reference reads out of bounds there
+
+
+def test_config4_batch_properties(oracle_port):
+    """BASELINE config 4 shape (stick-figure x 240 frames, D = 780, N_s = 1216) at a reduced candidate count
+    for the oracle comparison plus size-independent properties at the full 4096."""
+    scene = synthetic.stick_240(load_scene("stick-figure"))
+    c = Core(scene)
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    assert c.D == 780
+    B = 4096
+    X = synthetic.perturbed_candidates(x0, B)
+    f, terms = c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True)
+    assert np.isfinite(f).all() and (f > 0).all()
+    assert np.array_equal(f, terms[:, 0] + terms[:, 1] + terms[:, 2])
+    # permutation invariance / idempotence: rows are independent and deterministic
+    perm = np.random.default_rng(0).permutation(B)
+    f2 = c.CalculateFullObjectiveBatch(lo, hi, X[perm], x0)
+    assert np.array_equal(f2, f[perm])
+    # D_param is an exact quadratic form of x - x0 once weights are set; D_traj >= 0
+    c.UpdateGlobalWeight(12.5)
+    f3, t3 = c.CalculateFullObjectiveBatch(lo, hi, X[:64], x0, want_terms=True)
+    assert np.allclose(t3[:, 1], 12.5 * np.sum((X[:64] - x0) ** 2, axis=1), rtol=1e-13)
+    assert (t3[:, 2] >= 0).all() and np.allclose(t3[:, 0], terms[:64, 0], rtol=1e-15, atol=0)
+    f_same, t_same = c.CalculateFullObjective(lo, hi, x0, x0, want_terms=True)
+    assert t_same[1] == 0.0 and abs(t_same[2]) <= 1e-20
+    # oracle on a few rows
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1); o.set_weight_trajectory(12.5)
+    for b in (0, 17, 63):
+        fo, _ = o.full_objective(X[b], x0)
+        assert abs(f3[b] - fo) <= TOL * abs(fo)
+    # sharded gradient columns == monolithic gradient (the multi-GPU decomposition on one device)
+    eng = c.engine()
+    idx = c.free_indices()
+    f0, g, fpm = eng.eval_grad(X[1], idx, 1e-4)
+    P = 2 * idx.size + 1
+    cols = np.zeros(P)
+    d_out = eng.device_alloc(8 * P)
+    for r in range(3):
+        b, n = shard_range(P, r, 3)
+        eng.eval_grad_columns(X[1], idx, 1e-4, b, n, d_out, sync=True)
+        cols[b:b + n] = eng.d2h(d_out, (n,))
+    eng.device_free(d_out)
+    f0s, gs = grad_from_columns(cols, 1e-4)
+    assert f0s == f0 and np.array_equal(gs, g)
+
+
+def test_config5_tree_matches_oracle(oracle_port):
+    """BASELINE config 5 skeleton (64-joint binary tree, dense keys) on a short window."""
+    scene = synthetic.tree_scene(n_joints=64, n_frames=60)
+    c = Core(scene)
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1)
+    x0 = c.GetDescriptor()
+    X = synthetic.perturbed_candidates(x0, 3)
+    lo, hi = c.window
+    c.UpdateGlobalWeight(1.0); o.set_weight_trajectory(1.0)
+    f = c.CalculateFullObjectiveBatch(lo, hi, X, x0)
+    for b in range(3):
+        fo, _ = o.full_objective(X[b], x0)
+        assert abs(f[b] - fo) <= TOL * abs(fo), (f[b], fo)
+
+
+def test_counters_report_executed_curve_and_ik_work():
+    c = Core(scene_path("conductor"))
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    eng = c.engine(synced_window=(lo, hi))
+    eng.set_counting(True)
+    eng.eval(x0)
+    k = eng.counters()
+    eng.set_counting(False)
+    assert k["ik_solves"] == 220                        # one solve per time sample (N_s = 220)
+    assert 12 * 220 <= k["ik_iters"] <= 20 * 220
+    assert 0 < k["bezier_evals"] <= 220 * 4 and k["newton_iters"] >= k["bezier_evals"]
+    assert k["launches"] > 0
