@@ -126,6 +126,7 @@ def test_unsorted_chain_and_out_of_range_samples(oracle_port):
     assert abs(f - fo) <= TOL * abs(fo)
     # a window far outside every key: all curves clamp to their end values -> zero torque, zero cost
     f_far = c.CalculateFullObjective(100.0, 120.0, x0, x0)
+    o.update_original(x0)
     fo_far, _ = o.full_objective(x0, x0, window=(100.0, 120.0))
     assert abs(f_far - fo_far) <= 1e-12 and abs(f_far) < 1e-20
 
@@ -138,6 +139,7 @@ def test_small_windows_and_boundary_stencils(oracle_port):
     x0 = c.GetDescriptor()
     for hi in (10.45, 10.65, 10.85, 11.05, 35.0):
         f = c.CalculateFullObjective(10.0, hi, x0, x0)
+        o.update_original(x0)   # the reference's OriginalMotionCache is keyed on x_original only: reset it per window
         fo, _ = o.full_objective(x0, x0, window=(10.0, hi))
         assert abs(f - fo) <= TOL * abs(fo) + 1e-15, (hi, f, fo)
     with pytest.raises(EngineError):
