@@ -224,6 +224,9 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         }
     }
     if (pos != sc->n_cp) return fail(ctx, OMO_BAD_ARG, "n_cp does not match the channels' control points");
+    // joints frozen at zero angles take the identity fast path (E = I, qd = qdd = 0 exactly)
+    for (int j = 1; j < J; ++j)
+        S.ident[j] = (S.dyn[j] == 0 && S.chan_const[3 * j] == 0.0 && S.chan_const[3 * j + 1] == 0.0 && S.chan_const[3 * j + 2] == 0.0) ? 1 : 0;
 
     // IK handlers (ikhandler.cpp:45-67,77-101): chain = path root .. end effector
     for (int j = 0; j < J; ++j) { S.ik_of[j] = -1; S.ik_idx[j] = 0; S.ik_start[j] = -1; }
@@ -241,7 +244,7 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         S.ik_nb[h] = nb;
         for (int i = 0; i <= nb; ++i) S.ik_joint[h][i] = path[i];
         S.ik_start[root] = (short)h;
-        for (int i = 0; i < nb; ++i) { S.ik_of[path[i]] = (short)h; S.ik_idx[path[i]] = (short)i; }
+        for (int i = 0; i < nb; ++i) { S.ik_of[path[i]] = (short)h; S.ik_idx[path[i]] = (short)i; S.ident[path[i]] = 0; }
     }
     ctx->scene_dirty = true;
     omo_status st;

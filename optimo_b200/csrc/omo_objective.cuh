@@ -93,8 +93,10 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
             if (fs >= 0) {
                 OMO_STK(fs, 0) = f.w0; OMO_STK(fs, 1) = f.w1; OMO_STK(fs, 2) = f.w2;
                 OMO_STK(fs, 3) = f.l0; OMO_STK(fs, 4) = f.l1; OMO_STK(fs, 5) = f.l2;
-                OMO_STK(fs, 6) = s0; OMO_STK(fs, 7) = c0; OMO_STK(fs, 8) = s1;
-                OMO_STK(fs, 9) = c1; OMO_STK(fs, 10) = s2; OMO_STK(fs, 11) = c2;
+                if (!S.ident[b - 1]) {
+                    OMO_STK(fs, 6) = s0; OMO_STK(fs, 7) = c0; OMO_STK(fs, 8) = s1;
+                    OMO_STK(fs, 9) = c1; OMO_STK(fs, 10) = s2; OMO_STK(fs, 11) = c2;
+                }
             }
             if (va >= 0) {
                 OMO_STK(va, 0) = v.w0; OMO_STK(va, 1) = v.w1; OMO_STK(va, 2) = v.w2;
@@ -115,7 +117,8 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
             SV6 g;
             double t0, t1, t2;
             int k = b - 1;
-            rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
+            if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], f, g, t0, t1, t2);
+            else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
             tsq += t0 * t0 + t1 * t1 + t2 * t2;
             if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
             k = S.parent[k];
@@ -125,8 +128,9 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
                 SV6 fk_;
                 fk_.w0 = OMO_STK(fs, 0) + g.w0; fk_.w1 = OMO_STK(fs, 1) + g.w1; fk_.w2 = OMO_STK(fs, 2) + g.w2;
                 fk_.l0 = OMO_STK(fs, 3) + g.l0; fk_.l1 = OMO_STK(fs, 4) + g.l1; fk_.l2 = OMO_STK(fs, 5) + g.l2;
-                rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
-                              OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
+                if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], fk_, g, t0, t1, t2);
+                else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
+                                   OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
                 tsq += t0 * t0 + t1 * t1 + t2 * t2;
                 if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
                 k = S.parent[k];
@@ -180,7 +184,11 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
         double q0, q1, q2, qd0, qd1, qd2, qdd0, qdd1, qdd2;
         const int dyn = S.dyn[b];
         const int ikh = IK ? S.ik_of[b] : -1;
-        if (dyn == 0 && ikh < 0) {
+        const bool ident = S.ident[b] != 0;
+        if (ident) {
+            q0 = q1 = q2 = 0.0; qd0 = qd1 = qd2 = 0.0; qdd0 = qdd1 = qdd2 = 0.0;
+            s0 = s1 = s2 = 0.0; c0 = c1 = c2 = 1.0;
+        } else if (dyn == 0 && ikh < 0) {
             q0 = S.chan_const[3 * b]; q1 = S.chan_const[3 * b + 1]; q2 = S.chan_const[3 * b + 2];
             s0 = S.chan_sin[3 * b]; s1 = S.chan_sin[3 * b + 1]; s2 = S.chan_sin[3 * b + 2];
             c0 = S.chan_cos[3 * b]; c1 = S.chan_cos[3 * b + 1]; c2 = S.chan_cos[3 * b + 2];
@@ -241,7 +249,8 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
         // ---- forward dynamics step (v, a hold the parent's state on entry, the body's on exit) ----------
         {
             SV6 vn, an;
-            rnea_forward(S.body[b], s0, c0, s1, c1, s2, c2, qd0, qd1, qd2, qdd0, qdd1, qdd2, v, a, vn, an, f);
+            if (ident) rnea_forward_identity(S.body[b], v, a, vn, an, f);
+            else rnea_forward(S.body[b], s0, c0, s1, c1, s2, c2, qd0, qd1, qd2, qdd0, qdd1, qdd2, v, a, vn, an, f);
             v = vn; a = an;
         }
 
@@ -276,7 +285,8 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
         SV6 g;
         double t0, t1, t2;
         int k = J - 1;
-        rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
+        if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], f, g, t0, t1, t2);
+            else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
         tsq += t0 * t0 + t1 * t1 + t2 * t2;
         if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
         k = S.parent[k];
@@ -286,8 +296,9 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
             SV6 fk_;
             fk_.w0 = OMO_STK(fs, 0) + g.w0; fk_.w1 = OMO_STK(fs, 1) + g.w1; fk_.w2 = OMO_STK(fs, 2) + g.w2;
             fk_.l0 = OMO_STK(fs, 3) + g.l0; fk_.l1 = OMO_STK(fs, 4) + g.l1; fk_.l2 = OMO_STK(fs, 5) + g.l2;
-            rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
-                          OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
+            if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], fk_, g, t0, t1, t2);
+                else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
+                                   OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
             tsq += t0 * t0 + t1 * t1 + t2 * t2;
             if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
             k = S.parent[k];

@@ -34,6 +34,7 @@ struct OmoDevScene {
     short ik_start[OMO_MAXJ]; // IK handler whose chain root is this joint, -1 if none
     unsigned char n_child[OMO_MAXJ];
     unsigned char dyn[OMO_MAXJ];  // bit a: channel 3j+a is keyframed
+    unsigned char ident[OMO_MAXJ];  // 1: all three angles are the constant 0 and the joint is not IK-driven (E = I, qd = qdd = 0)
     // joint channels (3 per joint). pos = first position of the channel in the chain-ordered prepared arrays.
     int chan_pos[3 * OMO_MAXJ];
     int chan_n[3 * OMO_MAXJ];
