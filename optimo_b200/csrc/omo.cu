@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -23,6 +24,7 @@ constexpr int kBlockThreads = 128;
 
 struct omo_ctx {
     int device = 0;
+    int sm_count = 148;
     cudaStream_t stream = nullptr;
     std::string err;
 
@@ -228,6 +230,30 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
     for (int j = 1; j < J; ++j)
         S.ident[j] = (S.dyn[j] == 0 && S.chan_const[3 * j] == 0.0 && S.chan_const[3 * j + 1] == 0.0 && S.chan_const[3 * j + 2] == 0.0) ? 1 : 0;
 
+    // curve groups: bodies are packed greedily, a body's keyed channels never straddle two groups
+    {
+        int total = 0;
+        for (int j = 1; j < J; ++j) for (int a = 0; a < 3; ++a) total += (S.dyn[j] >> a) & 1;
+        const int G = std::max(3, std::min(total, 12));
+        int g = -1, used = G, n_list = 0;
+        for (int j = 0; j < J; ++j) S.grp_first[j] = -1;
+        for (int ch = 0; ch < 3 * J; ++ch) S.chan_row[ch] = -1;
+        for (int j = 1; j < J; ++j) {
+            const int nd = ((S.dyn[j] >> 0) & 1) + ((S.dyn[j] >> 1) & 1) + ((S.dyn[j] >> 2) & 1);
+            if (nd == 0) continue;
+            if (used + nd > G) { ++g; used = 0; S.grp_first[j] = (short)g; S.grp_begin[g] = (short)n_list; }
+            for (int a = 0; a < 3; ++a)
+                if ((S.dyn[j] >> a) & 1) {
+                    S.grp_list[n_list++] = (short)(3 * j + a);
+                    S.chan_row[3 * j + a] = (short)((g & 1) * G + used);
+                    ++used;
+                }
+        }
+        S.n_groups = g + 1;
+        S.grp_begin[S.n_groups] = (short)n_list;
+        S.n_ex_rows = (S.n_groups > 1) ? 2 * G : G;
+    }
+
     // IK handlers (ikhandler.cpp:45-67,77-101): chain = path root .. end effector
     for (int j = 0; j < J; ++j) { S.ik_of[j] = -1; S.ik_idx[j] = 0; S.ik_start[j] = -1; }
     for (int h = 0; h < sc->n_ik; ++h) {
@@ -292,44 +318,76 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
     return OMO_OK;
 }
 
-size_t smem_bytes(const omo_ctx* ctx, bool fk)
+struct LaunchPlan { int ns, n_tiles, t_out; size_t smem; };
+
+size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns)
 {
     const int slots = fk ? ctx->n_slots_fk : ctx->n_slots_nofk;
-    return (size_t)(6 + slots * OMO_SLOT) * kBlockThreads * sizeof(double);
+    const int ex_rows = ctx->hs.n_ex_rows + (ctx->n_ik > 0 ? 6 : 0);
+    return std::max((size_t)(ex_rows + slots * OMO_SLOT) * ns * kBlockThreads * sizeof(double), (size_t)64 * sizeof(double));
 }
 
-template <bool FK, bool IK, bool OUT>
-omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B)
+// Tiling of the time axis: a block covers ns*128 consecutive samples of one candidate, 4 of them halo.
+LaunchPlan make_plan(const omo_ctx* ctx, int B, bool fk, bool ik, bool out)
 {
-    const size_t smem = std::max(smem_bytes(ctx, FK), (size_t)64 * sizeof(double));
-    if (smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
-    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<FK, IK, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LaunchPlan p;
+    p.ns = 1;
+    if (!ik && !out) {
+        const int t2 = 2 * kBlockThreads - 4;
+        const int tiles2 = (ctx->N_s + t2 - 1) / t2;
+        // two samples per thread pay off once the grid still fills the machine and two blocks fit one SM
+        const char* force = std::getenv("OMO_NS");   // tuning knob: 1 or 2 samples per thread
+        const bool want2 = force ? (std::atoi(force) == 2) : false;
+        if (want2 && smem_bytes(ctx, fk, 2) <= (size_t)113 * 1024 && (long long)B * tiles2 >= 2LL * ctx->sm_count * 2) p.ns = 2;
+    }
+    const int t_max = p.ns * kBlockThreads - 4;
+    p.n_tiles = (ctx->N_s + t_max - 1) / t_max;
+    p.t_out = (ctx->N_s + p.n_tiles - 1) / p.n_tiles;
+    p.smem = smem_bytes(ctx, fk, p.ns);
+    return p;
+}
+
+template <int NS, bool FK, bool IK, bool OUT>
+omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B, const LaunchPlan& plan)
+{
+    if (plan.smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
+    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<NS, FK, IK, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing && !OUT) {
         OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
-    omo::objective_kernel<FK, IK, OUT><<<B * ctx->n_tiles, kBlockThreads, smem, ctx->stream>>>(P);
+    omo::objective_kernel<NS, FK, IK, OUT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
     OMO_CUDA(cudaGetLastError());
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1;
     return OMO_OK;
 }
 
-omo_status launch_objective(omo_ctx* ctx, const OmoEvalParams& P, int B, bool fk, bool out)
+// Launches the objective kernel over B candidates and the finish kernel that adds the tile partials.
+omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool out, double* d_f, double* d_terms)
 {
     const bool ik = ctx->n_ik > 0;
-    if (ik) fk = true;
-    if (out) return ik ? launch_objective_t<true, true, true>(ctx, P, B) : launch_objective_t<true, false, true>(ctx, P, B);
-    if (ik) return launch_objective_t<true, true, false>(ctx, P, B);
-    return fk ? launch_objective_t<true, false, false>(ctx, P, B) : launch_objective_t<false, false, false>(ctx, P, B);
+    if (ik || out) fk = true;
+    const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
+    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out;
+    omo_status st;
+    if (out) st = ik ? launch_objective_t<1, true, true, true>(ctx, P, B, plan) : launch_objective_t<1, true, false, true>(ctx, P, B, plan);
+    else if (ik) st = launch_objective_t<1, true, true, false>(ctx, P, B, plan);
+    else if (plan.ns == 2) st = fk ? launch_objective_t<2, true, false, false>(ctx, P, B, plan) : launch_objective_t<2, false, false, false>(ctx, P, B, plan);
+    else st = fk ? launch_objective_t<1, true, false, false>(ctx, P, B, plan) : launch_objective_t<1, false, false, false>(ctx, P, B, plan);
+    if (st != OMO_OK) return st;
+    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, d_f, d_terms);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return OMO_OK;
 }
 
 void fill_params(const omo_ctx* ctx, OmoEvalParams& P)
 {
     std::memset(&P, 0, sizeof(P));
     P.prep = ctx->d_prep; P.flags = ctx->d_flags; P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = ctx->d_partial;
-    P.N_s = ctx->N_s; P.n_tiles = ctx->n_tiles; P.T_out = ctx->T_out; P.n_cp = ctx->n_cp;
+    P.N_s = ctx->N_s; P.n_cp = ctx->n_cp;
     const double dt = ctx->dt;
     P.dt = dt; P.inv_dt = 1.0 / dt; P.inv_2dt = 1.0 / (2.0 * dt); P.inv_12dt = 1.0 / (12.0 * dt);
     P.inv_dt2 = 1.0 / (dt * dt); P.inv_2dt2 = 1.0 / (2.0 * dt * dt); P.inv_12dt2 = 1.0 / (12.0 * dt * dt);
@@ -377,11 +435,7 @@ omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig)
     fill_params(ctx, P);
     P.p_orig = with_p_orig ? ctx->d_p_orig : nullptr;
     P.o_q = ctx->d_oq; P.o_qd = ctx->d_oqd; P.o_qdd = ctx->d_oqdd; P.o_tau = ctx->d_otau; P.o_local = ctx->d_olocal; P.o_p = ctx->d_op;
-    if ((st = launch_objective(ctx, P, 1, true, true)) != OMO_OK) return st;
-    omo::finish_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, 1, ctx->n_tiles, ctx->d_f, ctx->d_terms);
-    OMO_CUDA(cudaGetLastError());
-    ctx->launches += 1;
-    return OMO_OK;
+    return launch_objective(ctx, P, 1, true, true, ctx->d_f, ctx->d_terms);
 }
 
 omo_status ensure_ready(omo_ctx* ctx)
@@ -424,11 +478,7 @@ omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, 
     fill_params(ctx, P);
     const bool fk = (ctx->w_traj != 0.0) || ctx->n_ik > 0;
     P.p_orig = (ctx->w_traj != 0.0) ? ctx->d_p_orig : nullptr;
-    if ((st = launch_objective(ctx, P, B, fk, false)) != OMO_OK) return st;
-    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, ctx->n_tiles, d_f, d_terms);
-    OMO_CUDA(cudaGetLastError());
-    ctx->launches += 1;
-    return OMO_OK;
+    return launch_objective(ctx, P, B, fk, false, d_f, d_terms);
 }
 
 }  // namespace
@@ -454,6 +504,7 @@ omo_status omo_create(const omo_scene_desc* scene, int device, omo_ctx** out)
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
         g_create_error = cudaGetErrorString(e); delete ctx; return OMO_CUDA_ERROR;
     }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     omo_status st = build_scene(ctx, scene);
     if (st == OMO_OK) {
         cudaError_t e2 = cudaMalloc((void**)&ctx->d_counters, 4 * sizeof(unsigned long long));

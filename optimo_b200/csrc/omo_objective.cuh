@@ -6,6 +6,11 @@
 //   Joint::GetAffineRelativeTo{Parent,World}  OptiMo/joint.cpp:64-83   (T(offset) Rz Ry Rx)
 //   Core::CalculateCost       core_rbdl.cpp:307-346          (local_cost = |tau[3:]|^2 dt, weight w(t))
 //   D_traj                    core_rbdl.cpp:387-398
+//
+// Template parameters: NS = time samples per thread (2 interleaves two independent dependency chains per
+// thread for the FP64 pipe and halves the per-body table / address overhead; 1 is the low-latency form for
+// small batches), FK = also run forward kinematics (positions; needed for D_traj and for IK), IK = scene has
+// IK chains, OUT = write the per-sample OptimizationCache arrays (single-candidate launches only).
 #ifndef OMO_OBJECTIVE_CUH
 #define OMO_OBJECTIVE_CUH
 
@@ -13,309 +18,414 @@
 
 namespace omo {
 
-#define OMO_STK(slot, comp) stk[((slot) * OMO_SLOT + (comp)) * NT + tid]
+template <bool FK> struct Smp {
+    SV6 v, a, f;                          // state of the body visited last (v, a: also the parent state for the next one)
+    double s0, c0, s1, c1, s2, c2;        // sin / cos of its Euler angles
+    double L[FK ? 9 : 1], W[FK ? 3 : 1];  // world affine handed to the next body's FK step
+    double tsq, dtr;                      // sum tau^2 (non-root DoFs), sum |p - p_original|^2
+    double t;                             // time of this sample
+    int s;                                // sample index (clamped into [0, N_s))
+    int idx;                              // position inside the block's window (exchange-buffer column)
+    bool owned, interior;
+};
 
-template <bool FK, bool IK, bool OUT>
-__global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
+#define OMO_STK(slot, comp, j) stk[(((slot) * OMO_SLOT + (comp)) * NS + (j)) * NT + tid]
+
+template <int NS, bool FK, bool IK, bool OUT>
+__global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const OmoEvalParams P)
 {
+    static_assert(!(IK && NS != 1), "IK scenes run one sample per thread");
     extern __shared__ double smem[];
     const OmoDevScene& S = c_scene;
     const int NT = blockDim.x;
     const int tid = threadIdx.x;
+    const int WIN = NS * NT;                    // samples in this block's window, halo included
     const int cand = blockIdx.x / P.n_tiles;
     const int tile = blockIdx.x - cand * P.n_tiles;
-    double* __restrict__ ex = smem;            // [2][3][NT] stencil exchange
-    double* __restrict__ stk = smem + 6 * NT;  // [n_slots][OMO_SLOT][NT]
-
+    const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);
+    double* __restrict__ ex = smem;                    // [ex_rows][WIN] stencil exchange: q of the dynamic channels
+    double* __restrict__ stk = smem + ex_rows * WIN;   // [n_slots][OMO_SLOT][NS][NT]
     const int N = P.N_s;
-    const int s_raw = tile * P.T_out - 2 + tid;
-    const int s = min(max(s_raw, 0), N - 1);
+    const int J = S.J;
     const int tile_end = min(N, (tile + 1) * P.T_out);
-    const bool owned = (tid >= 2) && (s_raw < tile_end) && (s_raw >= 0);
-    const bool interior = (s >= 2) && (s <= N - 3);
-    const double t = __ldg(P.tgrid + s);
     const double* __restrict__ pc = P.prep + (size_t)cand * 6 * P.n_cp;
     const bool sorted = (__ldg(P.flags + cand) & 1u) != 0u;
-    // stencil neighbours inside the block (clamped for the halo threads, whose results are unused)
-    const int im2 = max(tid - 2, 0), im1 = max(tid - 1, 0), ip1 = min(tid + 1, NT - 1), ip2 = min(tid + 2, NT - 1);
+    const size_t dof = (size_t)3 * J;
 
     unsigned n_bez = 0, n_newton = 0, n_iksolve = 0, n_ikiter = 0;
-    double tsq = 0.0;   // sum of tau^2 over the non-root DoFs
-    double dtr = 0.0;   // |p - p_original|^2
     double ikq[IK ? OMO_MAX_IK * 3 * OMO_MAX_IK_CHAIN : 1];
+    SV6 groot[OUT ? NS : 1];
+    Smp<FK> sm[NS];
 
-    // ---- root (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212) -------------
-    SV6 v, a, f;  // state of the body visited last
-    v.w0 = v.w1 = v.w2 = 0.0; a.w0 = a.w1 = a.w2 = 0.0;
-    v.l0 = interior ? S.root_qd[0] : 0.0; v.l1 = interior ? S.root_qd[1] : 0.0; v.l2 = interior ? S.root_qd[2] : 0.0;
-    a.l0 = interior ? S.root_qdd[0] : 0.0; a.l1 = interior ? S.root_qdd[1] : 0.0; a.l2 = interior ? S.root_qdd[2] : 0.0;
-    f.w0 = f.w1 = f.w2 = f.l0 = f.l1 = f.l2 = 0.0;
-    double s0 = 0.0, c0 = 1.0, s1 = 0.0, c1 = 1.0, s2 = 0.0, c2 = 1.0;
-    double L00 = 1, L01 = 0, L02 = 0, L10 = 0, L11 = 1, L12 = 0, L20 = 0, L21 = 0, L22 = 1, W0 = 0, W1 = 0, W2 = 0;  // world affine
-    SV6 groot; groot.w0 = groot.w1 = groot.w2 = groot.l0 = groot.l1 = groot.l2 = 0.0;
+    // root state (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212): v = (0, qd), a = (0, qdd)
+    auto set_root = [&](Smp<FK>& m) {
+        m.v.w0 = m.v.w1 = m.v.w2 = 0.0; m.a.w0 = m.a.w1 = m.a.w2 = 0.0;
+        m.v.l0 = m.interior ? S.root_qd[0] : 0.0; m.v.l1 = m.interior ? S.root_qd[1] : 0.0; m.v.l2 = m.interior ? S.root_qd[2] : 0.0;
+        m.a.l0 = m.interior ? S.root_qdd[0] : 0.0; m.a.l1 = m.interior ? S.root_qdd[1] : 0.0; m.a.l2 = m.interior ? S.root_qdd[2] : 0.0;
+    };
 
-    if (OUT && owned) {
-        for (int k = 0; k < 3; ++k) {
-            P.o_q[(size_t)s * 3 * S.J + k] = S.offset[0][k];
-            P.o_qd[(size_t)s * 3 * S.J + k] = interior ? S.root_qd[k] : 0.0;
-            P.o_qdd[(size_t)s * 3 * S.J + k] = interior ? S.root_qdd[k] : 0.0;
-        }
-    }
-    if (FK) {
-        // root world affine = T(offset) Rz Ry Rx with the root's own rot channels (joint.cpp:64-74)
-        double e[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
-            e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], t, sorted, n_bez, n_newton)
-                                       : S.chan_const[k];
-        double sx, cx, sy, cy, sz, cz;
-        sincos(e[0], &sx, &cx); sincos(e[1], &sy, &cy); sincos(e[2], &sz, &cz);
-        L00 = cz * cy; L01 = cz * sy * sx - sz * cx; L02 = cz * sy * cx + sz * sx;
-        L10 = sz * cy; L11 = sz * sy * sx + cz * cx; L12 = sz * sy * cx - cz * sx;
-        L20 = -sy;     L21 = cy * sx;                L22 = cy * cx;
-        W0 = S.offset[0][0]; W1 = S.offset[0][1]; W2 = S.offset[0][2];
-        if (P.p_orig) {
-            const double d0 = W0 - __ldg(P.p_orig + (size_t)0 * N + s), d1 = W1 - __ldg(P.p_orig + (size_t)1 * N + s),
-                         d2 = W2 - __ldg(P.p_orig + (size_t)2 * N + s);
-            dtr += d0 * d0 + d1 * d1 + d2 * d2;
+    for (int j = 0; j < NS; ++j) {
+        Smp<FK>& m = sm[j];
+        m.idx = tid + j * NT;
+        const int s_raw = tile * P.T_out - 2 + m.idx;
+        m.s = min(max(s_raw, 0), N - 1);
+        m.owned = (m.idx >= 2) && (s_raw < tile_end) && (s_raw >= 0);
+        m.interior = (m.s >= 2) && (m.s <= N - 3);
+        m.t = __ldg(P.tgrid + m.s);
+        m.tsq = 0.0; m.dtr = 0.0;
+        set_root(m);
+        m.f.w0 = m.f.w1 = m.f.w2 = m.f.l0 = m.f.l1 = m.f.l2 = 0.0;
+        m.s0 = m.s1 = m.s2 = 0.0; m.c0 = m.c1 = m.c2 = 1.0;
+        if (OUT) { groot[j].w0 = groot[j].w1 = groot[j].w2 = groot[j].l0 = groot[j].l1 = groot[j].l2 = 0.0; }
+        if (OUT && m.owned) {
+            for (int k = 0; k < 3; ++k) {
+                P.o_q[m.s * dof + k] = S.offset[0][k];
+                P.o_qd[m.s * dof + k] = m.interior ? S.root_qd[k] : 0.0;
+                P.o_qdd[m.s * dof + k] = m.interior ? S.root_qdd[k] : 0.0;
+            }
         }
-        if (OUT && owned && P.o_p) { P.o_p[(size_t)s * 3 * S.J] = W0; P.o_p[(size_t)s * 3 * S.J + 1] = W1; P.o_p[(size_t)s * 3 * S.J + 2] = W2; }
+        if (FK) {
+            // root world affine = T(offset) Rz Ry Rx with the root's own rot channels (joint.cpp:64-74)
+            double e[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], m.t, sorted, n_bez, n_newton)
+                                           : S.chan_const[k];
+            double sx, cx, sy, cy, sz, cz;
+            sincos(e[0], &sx, &cx); sincos(e[1], &sy, &cy); sincos(e[2], &sz, &cz);
+            m.L[0] = cz * cy; m.L[1] = cz * sy * sx - sz * cx; m.L[2] = cz * sy * cx + sz * sx;
+            m.L[3] = sz * cy; m.L[4] = sz * sy * sx + cz * cx; m.L[5] = sz * sy * cx - cz * sx;
+            m.L[6] = -sy;     m.L[7] = cy * sx;                m.L[8] = cy * cx;
+            m.W[0] = S.offset[0][0]; m.W[1] = S.offset[0][1]; m.W[2] = S.offset[0][2];
+            if (P.p_orig) {
+                const double d0 = m.W[0] - __ldg(P.p_orig + (size_t)0 * N + m.s), d1 = m.W[1] - __ldg(P.p_orig + (size_t)1 * N + m.s),
+                             d2 = m.W[2] - __ldg(P.p_orig + (size_t)2 * N + m.s);
+                m.dtr += d0 * d0 + d1 * d1 + d2 * d2;
+            }
+            if (OUT && m.owned && P.o_p) { P.o_p[m.s * dof] = m.W[0]; P.o_p[m.s * dof + 1] = m.W[1]; P.o_p[m.s * dof + 2] = m.W[2]; }
+        }
     }
+
+    // tau = S^T f of body k from (f, sincos); returns g = X_lambda^T f and books |tau|^2
+    auto finalize = [&](const int k, Smp<FK>& m, const SV6& fk, const double s0, const double c0, const double s1, const double c1,
+                        const double s2, const double c2, SV6& g) {
+        double t0, t1, t2;
+        const double r0 = S.body[k].r[0], r1 = S.body[k].r[1], r2 = S.body[k].r[2];
+        if (S.ident[k]) rnea_backward_identity(r0, r1, r2, fk, g, t0, t1, t2);
+        else rnea_backward(r0, r1, r2, s0, c0, s1, c1, s2, c2, fk, g, t0, t1, t2);
+        m.tsq = fma(t0, t0, fma(t1, t1, fma(t2, t2, m.tsq)));
+        if (OUT && m.owned) { P.o_tau[m.s * dof + 3 * k] = t0; P.o_tau[m.s * dof + 3 * k + 1] = t1; P.o_tau[m.s * dof + 3 * k + 2] = t2; }
+    };
+    // fold the finished leaf b_last and every finished ancestor back, stopping below `stop`
+    auto fold_back = [&](const int b_last, const int stop) {
+        SV6 g[NS];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) finalize(b_last, sm[j], sm[j].f, sm[j].s0, sm[j].c0, sm[j].s1, sm[j].c1, sm[j].s2, sm[j].c2, g[j]);
+        int k = S.parent[b_last];
+#pragma unroll 1
+        while (k != stop) {
+            const int fs = S.fs_slot[k];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                SV6 fk;
+                fk.w0 = OMO_STK(fs, 0, j) + g[j].w0; fk.w1 = OMO_STK(fs, 1, j) + g[j].w1; fk.w2 = OMO_STK(fs, 2, j) + g[j].w2;
+                fk.l0 = OMO_STK(fs, 3, j) + g[j].l0; fk.l1 = OMO_STK(fs, 4, j) + g[j].l1; fk.l2 = OMO_STK(fs, 5, j) + g[j].l2;
+                finalize(k, sm[j], fk, OMO_STK(fs, 6, j), OMO_STK(fs, 7, j), OMO_STK(fs, 8, j), OMO_STK(fs, 9, j), OMO_STK(fs, 10, j),
+                         OMO_STK(fs, 11, j), g[j]);
+            }
+            k = S.parent[k];
+        }
+        if (stop != 0) {
+            const int fs = S.fs_slot[stop];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                OMO_STK(fs, 0, j) += g[j].w0; OMO_STK(fs, 1, j) += g[j].w1; OMO_STK(fs, 2, j) += g[j].w2;
+                OMO_STK(fs, 3, j) += g[j].l0; OMO_STK(fs, 4, j) += g[j].l1; OMO_STK(fs, 5, j) += g[j].l2;
+            }
+        } else if (OUT) {
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                groot[j].w0 += g[j].w0; groot[j].w1 += g[j].w1; groot[j].w2 += g[j].w2;
+                groot[j].l0 += g[j].l0; groot[j].l1 += g[j].l1; groot[j].l2 += g[j].l2;
+            }
+        }
+    };
 
     int xbuf = 0;
-    const int J = S.J;
 #pragma unroll 1
     for (int b = 1; b < J; ++b) {
         const int par = S.parent[b];
-        // ---- leave body b-1: park it (descending) or fold the finished subtree(s) back ----------------
+        // ---- leave body b-1: park it (descending) or fold the finished subtree(s) back --------------------
         if (par == b - 1) {
             const int fs = S.fs_slot[b - 1], va = S.va_slot[b - 1];
             if (fs >= 0) {
-                OMO_STK(fs, 0) = f.w0; OMO_STK(fs, 1) = f.w1; OMO_STK(fs, 2) = f.w2;
-                OMO_STK(fs, 3) = f.l0; OMO_STK(fs, 4) = f.l1; OMO_STK(fs, 5) = f.l2;
-                if (!S.ident[b - 1]) {
-                    OMO_STK(fs, 6) = s0; OMO_STK(fs, 7) = c0; OMO_STK(fs, 8) = s1;
-                    OMO_STK(fs, 9) = c1; OMO_STK(fs, 10) = s2; OMO_STK(fs, 11) = c2;
+                const bool idp = S.ident[b - 1] != 0;
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+                    const Smp<FK>& m = sm[j];
+                    OMO_STK(fs, 0, j) = m.f.w0; OMO_STK(fs, 1, j) = m.f.w1; OMO_STK(fs, 2, j) = m.f.w2;
+                    OMO_STK(fs, 3, j) = m.f.l0; OMO_STK(fs, 4, j) = m.f.l1; OMO_STK(fs, 5, j) = m.f.l2;
+                    if (!idp) {
+                        OMO_STK(fs, 6, j) = m.s0; OMO_STK(fs, 7, j) = m.c0; OMO_STK(fs, 8, j) = m.s1;
+                        OMO_STK(fs, 9, j) = m.c1; OMO_STK(fs, 10, j) = m.s2; OMO_STK(fs, 11, j) = m.c2;
+                    }
                 }
             }
             if (va >= 0) {
-                OMO_STK(va, 0) = v.w0; OMO_STK(va, 1) = v.w1; OMO_STK(va, 2) = v.w2;
-                OMO_STK(va, 3) = v.l0; OMO_STK(va, 4) = v.l1; OMO_STK(va, 5) = v.l2;
-                OMO_STK(va, 6) = a.w0; OMO_STK(va, 7) = a.w1; OMO_STK(va, 8) = a.w2;
-                OMO_STK(va, 9) = a.l0; OMO_STK(va, 10) = a.l1; OMO_STK(va, 11) = a.l2;
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+                    const Smp<FK>& m = sm[j];
+                    OMO_STK(va, 0, j) = m.v.w0; OMO_STK(va, 1, j) = m.v.w1; OMO_STK(va, 2, j) = m.v.w2;
+                    OMO_STK(va, 3, j) = m.v.l0; OMO_STK(va, 4, j) = m.v.l1; OMO_STK(va, 5, j) = m.v.l2;
+                    OMO_STK(va, 6, j) = m.a.w0; OMO_STK(va, 7, j) = m.a.w1; OMO_STK(va, 8, j) = m.a.w2;
+                    OMO_STK(va, 9, j) = m.a.l0; OMO_STK(va, 10, j) = m.a.l1; OMO_STK(va, 11, j) = m.a.l2;
+                }
             }
             if (FK) {
                 const int fk = S.fk_slot[b - 1];
                 if (fk >= 0) {
-                    OMO_STK(fk, 0) = L00; OMO_STK(fk, 1) = L01; OMO_STK(fk, 2) = L02;
-                    OMO_STK(fk, 3) = L10; OMO_STK(fk, 4) = L11; OMO_STK(fk, 5) = L12;
-                    OMO_STK(fk, 6) = L20; OMO_STK(fk, 7) = L21; OMO_STK(fk, 8) = L22;
-                    OMO_STK(fk, 9) = W0; OMO_STK(fk, 10) = W1; OMO_STK(fk, 11) = W2;
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+#pragma unroll
+                        for (int c = 0; c < 9; ++c) OMO_STK(fk, c, j) = sm[j].L[c];
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) OMO_STK(fk, 9 + c, j) = sm[j].W[c];
+                    }
                 }
             }
         } else {
-            SV6 g;
-            double t0, t1, t2;
-            int k = b - 1;
-            if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], f, g, t0, t1, t2);
-            else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
-            tsq += t0 * t0 + t1 * t1 + t2 * t2;
-            if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
-            k = S.parent[k];
-#pragma unroll 1
-            while (k != par) {
-                const int fs = S.fs_slot[k];
-                SV6 fk_;
-                fk_.w0 = OMO_STK(fs, 0) + g.w0; fk_.w1 = OMO_STK(fs, 1) + g.w1; fk_.w2 = OMO_STK(fs, 2) + g.w2;
-                fk_.l0 = OMO_STK(fs, 3) + g.l0; fk_.l1 = OMO_STK(fs, 4) + g.l1; fk_.l2 = OMO_STK(fs, 5) + g.l2;
-                if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], fk_, g, t0, t1, t2);
-                else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
-                                   OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
-                tsq += t0 * t0 + t1 * t1 + t2 * t2;
-                if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
-                k = S.parent[k];
-            }
-            if (par != 0) {
-                const int fs = S.fs_slot[par];
-                OMO_STK(fs, 0) += g.w0; OMO_STK(fs, 1) += g.w1; OMO_STK(fs, 2) += g.w2;
-                OMO_STK(fs, 3) += g.l0; OMO_STK(fs, 4) += g.l1; OMO_STK(fs, 5) += g.l2;
-            } else if (OUT) {
-                groot.w0 += g.w0; groot.w1 += g.w1; groot.w2 += g.w2; groot.l0 += g.l0; groot.l1 += g.l1; groot.l2 += g.l2;
-            }
+            fold_back(b - 1, par);
             // parent state for b (the root's is a function of the sample index only: recomputed, not parked)
             if (par == 0) {
-                v.w0 = v.w1 = v.w2 = 0.0; a.w0 = a.w1 = a.w2 = 0.0;
-                v.l0 = interior ? S.root_qd[0] : 0.0; v.l1 = interior ? S.root_qd[1] : 0.0; v.l2 = interior ? S.root_qd[2] : 0.0;
-                a.l0 = interior ? S.root_qdd[0] : 0.0; a.l1 = interior ? S.root_qdd[1] : 0.0; a.l2 = interior ? S.root_qdd[2] : 0.0;
+#pragma unroll
+                for (int j = 0; j < NS; ++j) set_root(sm[j]);
             } else {
                 const int va = S.va_slot[par];
-                v.w0 = OMO_STK(va, 0); v.w1 = OMO_STK(va, 1); v.w2 = OMO_STK(va, 2);
-                v.l0 = OMO_STK(va, 3); v.l1 = OMO_STK(va, 4); v.l2 = OMO_STK(va, 5);
-                a.w0 = OMO_STK(va, 6); a.w1 = OMO_STK(va, 7); a.w2 = OMO_STK(va, 8);
-                a.l0 = OMO_STK(va, 9); a.l1 = OMO_STK(va, 10); a.l2 = OMO_STK(va, 11);
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+                    Smp<FK>& m = sm[j];
+                    m.v.w0 = OMO_STK(va, 0, j); m.v.w1 = OMO_STK(va, 1, j); m.v.w2 = OMO_STK(va, 2, j);
+                    m.v.l0 = OMO_STK(va, 3, j); m.v.l1 = OMO_STK(va, 4, j); m.v.l2 = OMO_STK(va, 5, j);
+                    m.a.w0 = OMO_STK(va, 6, j); m.a.w1 = OMO_STK(va, 7, j); m.a.w2 = OMO_STK(va, 8, j);
+                    m.a.l0 = OMO_STK(va, 9, j); m.a.l1 = OMO_STK(va, 10, j); m.a.l2 = OMO_STK(va, 11, j);
+                }
             }
             if (FK) {
                 const int fk = S.fk_slot[par];
-                L00 = OMO_STK(fk, 0); L01 = OMO_STK(fk, 1); L02 = OMO_STK(fk, 2);
-                L10 = OMO_STK(fk, 3); L11 = OMO_STK(fk, 4); L12 = OMO_STK(fk, 5);
-                L20 = OMO_STK(fk, 6); L21 = OMO_STK(fk, 7); L22 = OMO_STK(fk, 8);
-                W0 = OMO_STK(fk, 9); W1 = OMO_STK(fk, 10); W2 = OMO_STK(fk, 11);
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+#pragma unroll
+                    for (int c = 0; c < 9; ++c) sm[j].L[c] = OMO_STK(fk, c, j);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) sm[j].W[c] = OMO_STK(fk, 9 + c, j);
+                }
             }
         }
 
-        // ---- IK chains rooted here: solve once per sample (joint.cpp:38-44, ikhandler.cpp:103-164) ------
+        // ---- IK chains rooted here: solve once per sample (joint.cpp:38-44, ikhandler.cpp:103-164) ----------
         if (IK) {
             const int h = S.ik_start[b];
             if (h >= 0) {
+                Smp<FK>& m = sm[0];
                 double tw[3];
 #pragma unroll
                 for (int k = 0; k < 3; ++k)
                     tw[k] = (S.ik_chan_n[h][k] > 0)
-                                ? eval_channel(pc, P.n_cp, S.ik_chan_pos[h][k], S.ik_chan_n[h][k], t, sorted, n_bez, n_newton)
+                                ? eval_channel(pc, P.n_cp, S.ik_chan_pos[h][k], S.ik_chan_n[h][k], m.t, sorted, n_bez, n_newton)
                                 : S.ik_chan_const[h][k];
-                const double Lp[9] = {L00, L01, L02, L10, L11, L12, L20, L21, L22};
-                const double tp[3] = {W0, W1, W2};
-                ik_solve(h, Lp, tp, tw, ikq + h * 3 * OMO_MAX_IK_CHAIN, n_ikiter);
-                n_iksolve += 1u;
+                double Lp[9], tp[3];
+#pragma unroll
+                for (int c = 0; c < 9; ++c) Lp[c] = FK ? m.L[c] : 0.0;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) tp[c] = FK ? m.W[c] : 0.0;
+                unsigned it = 0;
+                ik_solve(h, Lp, tp, tw, ikq + h * 3 * OMO_MAX_IK_CHAIN, it);
+                if (m.owned) { n_ikiter += it; n_iksolve += 1u; }
             }
         }
 
-        // ---- angles of body b, their time derivatives, sin/cos ------------------------------------------
-        double q0, q1, q2, qd0, qd1, qd2, qdd0, qdd1, qdd2;
+        // ---- curve group starting here: sample its keyed channels for this thread's times (K-way interleaved) ----
+        {
+            const int g = S.grp_first[b];
+            if (g >= 0) {
+                const int g0 = S.grp_begin[g], g1 = S.grp_begin[g + 1];
+#pragma unroll 1
+                for (int c0 = g0; c0 < g1; c0 += 3) {
+                    int pos[3], nn[3], row[3];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const bool on = c0 + k < g1;
+                        const int ch = on ? S.grp_list[c0 + k] : 0;
+                        pos[k] = on ? S.chan_pos[ch] : 0; nn[k] = on ? S.chan_n[ch] : 0; row[k] = on ? S.chan_row[ch] : 0;
+                    }
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+                        double val[3];
+                        unsigned eb = 0, en = 0;
+                        eval_channels<3>(pc, P.n_cp, pos, nn, sm[j].t, sorted, val, eb, en);
+                        if (sm[j].owned) { n_bez += eb; n_newton += en; }   // halo samples repeat a neighbour tile's work
+#pragma unroll
+                        for (int k = 0; k < 3; ++k)
+                            if (nn[k] > 0) ex[row[k] * WIN + sm[j].idx] = val[k];
+                    }
+                }
+                __syncthreads();
+            }
+        }
+
+        // ---- angles of body b, their time derivatives, sin/cos ------------------------------------------------
         const int dyn = S.dyn[b];
         const int ikh = IK ? S.ik_of[b] : -1;
         const bool ident = S.ident[b] != 0;
+        double q[NS][3], qd[NS][3], qdd[NS][3];
         if (ident) {
-            q0 = q1 = q2 = 0.0; qd0 = qd1 = qd2 = 0.0; qdd0 = qdd1 = qdd2 = 0.0;
-            s0 = s1 = s2 = 0.0; c0 = c1 = c2 = 1.0;
-        } else if (dyn == 0 && ikh < 0) {
-            q0 = S.chan_const[3 * b]; q1 = S.chan_const[3 * b + 1]; q2 = S.chan_const[3 * b + 2];
-            s0 = S.chan_sin[3 * b]; s1 = S.chan_sin[3 * b + 1]; s2 = S.chan_sin[3 * b + 2];
-            c0 = S.chan_cos[3 * b]; c1 = S.chan_cos[3 * b + 1]; c2 = S.chan_cos[3 * b + 2];
-            qd0 = interior ? S.chan_qd[3 * b] : 0.0; qd1 = interior ? S.chan_qd[3 * b + 1] : 0.0; qd2 = interior ? S.chan_qd[3 * b + 2] : 0.0;
-            qdd0 = interior ? S.chan_qdd[3 * b] : 0.0; qdd1 = interior ? S.chan_qdd[3 * b + 1] : 0.0; qdd2 = interior ? S.chan_qdd[3 * b + 2] : 0.0;
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { q[j][k] = 0.0; qd[j][k] = 0.0; qdd[j][k] = 0.0; }
+                sm[j].s0 = sm[j].s1 = sm[j].s2 = 0.0; sm[j].c0 = sm[j].c1 = sm[j].c2 = 1.0;
+            }
         } else {
-            double qq[3], qqd[3], qqdd[3], ss[3], cc[3];
             const int mask = (ikh >= 0) ? 7 : dyn;
-            double* __restrict__ exb = ex + xbuf * 3 * NT;
+            double ss[NS][3], cc[NS][3];
+            int rowk[3];
+            if (IK && ikh >= 0) {
+                // IK-driven joint: its angles were solved per thread; exchange them through 3 dedicated double-buffered rows
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (mask >> k & 1) {
-                    if (IK && ikh >= 0) qq[k] = ikq[ikh * 3 * OMO_MAX_IK_CHAIN + 3 * S.ik_idx[b] + k];
-                    else qq[k] = eval_channel(pc, P.n_cp, S.chan_pos[3 * b + k], S.chan_n[3 * b + k], t, sorted, n_bez, n_newton);
-                    exb[k * NT + tid] = qq[k];
+                for (int k = 0; k < 3; ++k) {
+                    rowk[k] = S.n_ex_rows + xbuf * 3 + k;
+                    ex[rowk[k] * WIN + sm[0].idx] = ikq[ikh * 3 * OMO_MAX_IK_CHAIN + 3 * S.ik_idx[b] + k];
                 }
+                __syncthreads();
+                xbuf ^= 1;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) rowk[k] = (mask >> k & 1) ? S.chan_row[3 * b + k] : 0;
             }
-            __syncthreads();
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 if (mask >> k & 1) {
-                    const double m2 = exb[k * NT + im2], m1 = exb[k * NT + im1], p1 = exb[k * NT + ip1], p2 = exb[k * NT + ip2];
-                    const double x = qq[k];
-                    if (interior) {
-                        qqd[k] = (-p2 + 8.0 * p1 - 8.0 * m1 + m2) * P.inv_12dt;
-                        qqdd[k] = (-p2 + 16.0 * p1 - 30.0 * x + 16.0 * m1 - m2) * P.inv_12dt2;
-                    } else if (s == 0) {
-                        qqd[k] = (p1 - x) * P.inv_dt;
-                        qqdd[k] = (p2 - 2.0 * p1 + x) * P.inv_2dt2;
-                    } else if (s == N - 1) {
-                        qqd[k] = (x - m1) * P.inv_dt;
-                        qqdd[k] = (x - 2.0 * m1 + m2) * P.inv_2dt2;
-                    } else {
-                        qqd[k] = (p1 - m1) * P.inv_2dt;
-                        qqdd[k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
+                    const double* __restrict__ row = ex + rowk[k] * WIN;
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+                        const Smp<FK>& m = sm[j];
+                        // stencil neighbours inside the block (clamped for the halo samples, whose results are unused)
+                        const double m2 = row[max(m.idx - 2, 0)], m1 = row[max(m.idx - 1, 0)], x = row[m.idx];
+                        const double p1 = row[min(m.idx + 1, WIN - 1)], p2 = row[min(m.idx + 2, WIN - 1)];
+                        q[j][k] = x;
+                        if (m.interior) {
+                            qd[j][k] = (-p2 + 8.0 * p1 - 8.0 * m1 + m2) * P.inv_12dt;
+                            qdd[j][k] = (-p2 + 16.0 * p1 - 30.0 * x + 16.0 * m1 - m2) * P.inv_12dt2;
+                        } else if (m.s == 0) {
+                            qd[j][k] = (p1 - x) * P.inv_dt;
+                            qdd[j][k] = (p2 - 2.0 * p1 + x) * P.inv_2dt2;
+                        } else if (m.s == N - 1) {
+                            qd[j][k] = (x - m1) * P.inv_dt;
+                            qdd[j][k] = (x - 2.0 * m1 + m2) * P.inv_2dt2;
+                        } else {
+                            qd[j][k] = (p1 - m1) * P.inv_2dt;
+                            qdd[j][k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
+                        }
+                        sincos(x, &ss[j][k], &cc[j][k]);
                     }
-                    sincos(x, &ss[k], &cc[k]);
                 } else {
-                    qq[k] = S.chan_const[3 * b + k];
-                    ss[k] = S.chan_sin[3 * b + k]; cc[k] = S.chan_cos[3 * b + k];
-                    qqd[k] = interior ? S.chan_qd[3 * b + k] : 0.0;
-                    qqdd[k] = interior ? S.chan_qdd[3 * b + k] : 0.0;
+                    const double qc = S.chan_const[3 * b + k], sc_ = S.chan_sin[3 * b + k], cc_ = S.chan_cos[3 * b + k];
+                    const double rd = S.chan_qd[3 * b + k], rdd = S.chan_qdd[3 * b + k];
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+                        q[j][k] = qc; ss[j][k] = sc_; cc[j][k] = cc_;
+                        qd[j][k] = sm[j].interior ? rd : 0.0;
+                        qdd[j][k] = sm[j].interior ? rdd : 0.0;
+                    }
                 }
             }
-            xbuf ^= 1;
-            q0 = qq[0]; q1 = qq[1]; q2 = qq[2];
-            qd0 = qqd[0]; qd1 = qqd[1]; qd2 = qqd[2];
-            qdd0 = qqdd[0]; qdd1 = qqdd[1]; qdd2 = qqdd[2];
-            s0 = ss[0]; s1 = ss[1]; s2 = ss[2]; c0 = cc[0]; c1 = cc[1]; c2 = cc[2];
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                sm[j].s0 = ss[j][0]; sm[j].s1 = ss[j][1]; sm[j].s2 = ss[j][2];
+                sm[j].c0 = cc[j][0]; sm[j].c1 = cc[j][1]; sm[j].c2 = cc[j][2];
+            }
         }
-        if (OUT && owned) {
-            const size_t o = (size_t)s * 3 * J + 3 * b;
-            P.o_q[o] = q0; P.o_q[o + 1] = q1; P.o_q[o + 2] = q2;
-            P.o_qd[o] = qd0; P.o_qd[o + 1] = qd1; P.o_qd[o + 2] = qd2;
-            P.o_qdd[o] = qdd0; P.o_qdd[o + 1] = qdd1; P.o_qdd[o + 2] = qdd2;
+        if (OUT) {
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                if (!sm[j].owned) continue;
+                const size_t o = sm[j].s * dof + 3 * b;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { P.o_q[o + k] = q[j][k]; P.o_qd[o + k] = qd[j][k]; P.o_qdd[o + k] = qdd[j][k]; }
+            }
         }
 
-        // ---- forward dynamics step (v, a hold the parent's state on entry, the body's on exit) ----------
-        {
+        // ---- forward dynamics step (v, a hold the parent's state on entry, the body's on exit) ------------------
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            Smp<FK>& m = sm[j];
             SV6 vn, an;
-            if (ident) rnea_forward_identity(S.body[b], v, a, vn, an, f);
-            else rnea_forward(S.body[b], s0, c0, s1, c1, s2, c2, qd0, qd1, qd2, qdd0, qdd1, qdd2, v, a, vn, an, f);
-            v = vn; a = an;
+            if (ident) rnea_forward_identity(S.body[b], m.v, m.a, vn, an, m.f);
+            else rnea_forward(S.body[b], m.s0, m.c0, m.s1, m.c1, m.s2, m.c2, qd[j][0], qd[j][1], qd[j][2], qdd[j][0], qdd[j][1], qdd[j][2],
+                              m.v, m.a, vn, an, m.f);
+            m.v = vn; m.a = an;
         }
 
-        // ---- forward kinematics: p_b and the world affine handed to b's children --------------------------
+        // ---- forward kinematics: p_b and the world affine handed to b's children ----------------------------------
         if (FK) {
             const double o0 = S.offset[b][0], o1 = S.offset[b][1], o2 = S.offset[b][2];
-            const double p0 = L00 * o0 + L01 * o1 + L02 * o2 + W0;
-            const double p1 = L10 * o0 + L11 * o1 + L12 * o2 + W1;
-            const double p2 = L20 * o0 + L21 * o1 + L22 * o2 + W2;
-            if (P.p_orig) {
-                const double d0 = p0 - __ldg(P.p_orig + (size_t)(3 * b) * N + s), d1 = p1 - __ldg(P.p_orig + (size_t)(3 * b + 1) * N + s),
-                             d2 = p2 - __ldg(P.p_orig + (size_t)(3 * b + 2) * N + s);
-                dtr += d0 * d0 + d1 * d1 + d2 * d2;
-            }
-            if (OUT && owned && P.o_p) { P.o_p[(size_t)s * 3 * J + 3 * b] = p0; P.o_p[(size_t)s * 3 * J + 3 * b + 1] = p1; P.o_p[(size_t)s * 3 * J + 3 * b + 2] = p2; }
-            if (S.n_child[b] > 0) {
-                // R = Rz(q2) Ry(q1) Rx(q0)
-                const double R00 = c2 * c1, R01 = c2 * s1 * s0 - s2 * c0, R02 = c2 * s1 * c0 + s2 * s0;
-                const double R10 = s2 * c1, R11 = s2 * s1 * s0 + c2 * c0, R12 = s2 * s1 * c0 - c2 * s0;
-                const double R20 = -s1, R21 = c1 * s0, R22 = c1 * c0;
-                const double n00 = L00 * R00 + L01 * R10 + L02 * R20, n01 = L00 * R01 + L01 * R11 + L02 * R21, n02 = L00 * R02 + L01 * R12 + L02 * R22;
-                const double n10 = L10 * R00 + L11 * R10 + L12 * R20, n11 = L10 * R01 + L11 * R11 + L12 * R21, n12 = L10 * R02 + L11 * R12 + L12 * R22;
-                const double n20 = L20 * R00 + L21 * R10 + L22 * R20, n21 = L20 * R01 + L21 * R11 + L22 * R21, n22 = L20 * R02 + L21 * R12 + L22 * R22;
-                L00 = n00; L01 = n01; L02 = n02; L10 = n10; L11 = n11; L12 = n12; L20 = n20; L21 = n21; L22 = n22;
-                W0 = p0; W1 = p1; W2 = p2;
+            const bool has_child = S.n_child[b] > 0;
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                Smp<FK>& m = sm[j];
+                const double p0 = fma(m.L[0], o0, fma(m.L[1], o1, fma(m.L[2], o2, m.W[0])));
+                const double p1 = fma(m.L[3], o0, fma(m.L[4], o1, fma(m.L[5], o2, m.W[1])));
+                const double p2 = fma(m.L[6], o0, fma(m.L[7], o1, fma(m.L[8], o2, m.W[2])));
+                if (P.p_orig) {
+                    const double d0 = p0 - __ldg(P.p_orig + (size_t)(3 * b) * N + m.s), d1 = p1 - __ldg(P.p_orig + (size_t)(3 * b + 1) * N + m.s),
+                                 d2 = p2 - __ldg(P.p_orig + (size_t)(3 * b + 2) * N + m.s);
+                    m.dtr += d0 * d0 + d1 * d1 + d2 * d2;
+                }
+                if (OUT && m.owned && P.o_p) { P.o_p[m.s * dof + 3 * b] = p0; P.o_p[m.s * dof + 3 * b + 1] = p1; P.o_p[m.s * dof + 3 * b + 2] = p2; }
+                if (has_child) {
+                    if (!ident) {
+                        // L <- L * Rz(q2) Ry(q1) Rx(q0)
+                        const double s0 = m.s0, c0 = m.c0, s1 = m.s1, c1 = m.c1, s2 = m.s2, c2 = m.c2;
+                        const double R00 = c2 * c1, R01 = c2 * s1 * s0 - s2 * c0, R02 = c2 * s1 * c0 + s2 * s0;
+                        const double R10 = s2 * c1, R11 = s2 * s1 * s0 + c2 * c0, R12 = s2 * s1 * c0 - c2 * s0;
+                        const double R20 = -s1, R21 = c1 * s0, R22 = c1 * c0;
+                        double n[9];
+#pragma unroll
+                        for (int r = 0; r < 3; ++r) {
+                            n[3 * r] = fma(m.L[3 * r], R00, fma(m.L[3 * r + 1], R10, m.L[3 * r + 2] * R20));
+                            n[3 * r + 1] = fma(m.L[3 * r], R01, fma(m.L[3 * r + 1], R11, m.L[3 * r + 2] * R21));
+                            n[3 * r + 2] = fma(m.L[3 * r], R02, fma(m.L[3 * r + 1], R12, m.L[3 * r + 2] * R22));
+                        }
+#pragma unroll
+                        for (int c = 0; c < 9; ++c) m.L[c] = n[c];
+                    }
+                    m.W[0] = p0; m.W[1] = p1; m.W[2] = p2;
+                }
             }
         }
     }
 
-    // ---- fold everything that is still open back to the root -------------------------------------------
-    if (J > 1) {
-        SV6 g;
-        double t0, t1, t2;
-        int k = J - 1;
-        if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], f, g, t0, t1, t2);
-            else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], s0, c0, s1, c1, s2, c2, f, g, t0, t1, t2);
-        tsq += t0 * t0 + t1 * t1 + t2 * t2;
-        if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
-        k = S.parent[k];
-#pragma unroll 1
-        while (k != 0) {
-            const int fs = S.fs_slot[k];
-            SV6 fk_;
-            fk_.w0 = OMO_STK(fs, 0) + g.w0; fk_.w1 = OMO_STK(fs, 1) + g.w1; fk_.w2 = OMO_STK(fs, 2) + g.w2;
-            fk_.l0 = OMO_STK(fs, 3) + g.l0; fk_.l1 = OMO_STK(fs, 4) + g.l1; fk_.l2 = OMO_STK(fs, 5) + g.l2;
-            if (S.ident[k]) rnea_backward_identity(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], fk_, g, t0, t1, t2);
-                else rnea_backward(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], OMO_STK(fs, 6), OMO_STK(fs, 7), OMO_STK(fs, 8),
-                                   OMO_STK(fs, 9), OMO_STK(fs, 10), OMO_STK(fs, 11), fk_, g, t0, t1, t2);
-            tsq += t0 * t0 + t1 * t1 + t2 * t2;
-            if (OUT && owned) { P.o_tau[(size_t)s * 3 * J + 3 * k] = t0; P.o_tau[(size_t)s * 3 * J + 3 * k + 1] = t1; P.o_tau[(size_t)s * 3 * J + 3 * k + 2] = t2; }
-            k = S.parent[k];
-        }
-        if (OUT) { groot.w0 += g.w0; groot.w1 += g.w1; groot.w2 += g.w2; groot.l0 += g.l0; groot.l1 += g.l1; groot.l2 += g.l2; }
-    }
+    // ---- fold everything that is still open back to the root ------------------------------------------------------
+    if (J > 1) fold_back(J - 1, 0);
 
-    // ---- cost of this sample and block reduction (local_cost = |tau[3:]|^2 dt, core_rbdl.cpp:331-334) ------
-    const double local = tsq * P.dt;
-    if (OUT && owned) {
-        // tau[0:3] of the TranslationXYZ root = linear part of the force folded into body 1 (Dynamics.cc:91-92)
-        P.o_tau[(size_t)s * 3 * J] = groot.l0; P.o_tau[(size_t)s * 3 * J + 1] = groot.l1; P.o_tau[(size_t)s * 3 * J + 2] = groot.l2;
-        P.o_local[s] = local;
+    // ---- cost of the samples and block reduction (local_cost = |tau[3:]|^2 dt, core_rbdl.cpp:331-334) ---------------
+    double wc = 0.0, wt = 0.0;
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+        const Smp<FK>& m = sm[j];
+        const double local = m.tsq * P.dt;
+        if (OUT && m.owned) {
+            // tau[0:3] of the TranslationXYZ root = linear part of the force folded into body 1 (Dynamics.cc:91-92)
+            P.o_tau[m.s * dof] = groot[j].l0; P.o_tau[m.s * dof + 1] = groot[j].l1; P.o_tau[m.s * dof + 2] = groot[j].l2;
+            P.o_local[m.s] = local;
+        }
+        if (m.owned) {
+            wc += __ldg(P.wcost + m.s) * local;
+            if (FK) wt += P.w_traj * m.dtr * P.dt;
+        }
     }
-    double wc = owned ? __ldg(P.wcost + s) * local : 0.0;
-    double wt = (FK && owned) ? P.w_traj * dtr * P.dt : 0.0;
-    __syncthreads();  // everyone is done with smem
+    __syncthreads();  // everyone is done with the exchange buffers
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         wc += __shfl_down_sync(0xffffffffu, wc, o);
@@ -331,7 +441,7 @@ __global__ void __launch_bounds__(128) objective_kernel(const OmoEvalParams P)
         P.partial[(size_t)blockIdx.x * 2 + 1] = D;
     }
     if (P.counters) {
-        unsigned cb = owned ? n_bez : 0u, cn = owned ? n_newton : 0u, ci = owned ? n_iksolve : 0u, cj = owned ? n_ikiter : 0u;
+        unsigned cb = n_bez, cn = n_newton, ci = n_iksolve, cj = n_ikiter;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             cb += __shfl_down_sync(0xffffffffu, cb, o); cn += __shfl_down_sync(0xffffffffu, cn, o);

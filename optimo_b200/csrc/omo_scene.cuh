@@ -24,6 +24,8 @@ struct OmoBody {
 struct OmoDevScene {
     int J, n_ik;
     int n_slots;  // stack slots per thread (each OMO_SLOT doubles)
+    int n_groups;   // curve groups: keyed joint channels are sampled group by group, one block barrier per group
+    int n_ex_rows;  // rows of the stencil exchange buffer (2 * group size when there are several groups)
     int pad0;
     int parent[OMO_MAXJ];
     short fs_slot[OMO_MAXJ];  // slot of (f, sincos) while the body's subtree is open; -1 for leaves and the root
@@ -35,6 +37,10 @@ struct OmoDevScene {
     unsigned char n_child[OMO_MAXJ];
     unsigned char dyn[OMO_MAXJ];  // bit a: channel 3j+a is keyframed
     unsigned char ident[OMO_MAXJ];  // 1: all three angles are the constant 0 and the joint is not IK-driven (E = I, qd = qdd = 0)
+    short grp_first[OMO_MAXJ];        // group that starts at this body, -1 if none
+    short grp_begin[OMO_MAXJ + 1];    // group g owns grp_list[grp_begin[g] .. grp_begin[g+1])
+    short grp_list[3 * OMO_MAXJ];     // keyed joint channels (3*j + axis, j >= 1) in body order
+    short chan_row[3 * OMO_MAXJ];     // exchange row of a keyed joint channel (parity offset included), -1 otherwise
     // joint channels (3 per joint). pos = first position of the channel in the chain-ordered prepared arrays.
     int chan_pos[3 * OMO_MAXJ];
     int chan_n[3 * OMO_MAXJ];
