@@ -71,6 +71,11 @@ void optimo_set_stop_optimization(void* h, int flag);     /* Core::stop_optimiza
 int optimo_get_stop_optimization(void* h);
 int optimo_perform_optimization(void* h, int explicit_termination, double* final_value, int* evals);  /* core_opt.cpp:60-157 */
 
+/* Record of the last solve's callbacks in call order (rows x (dim + 1): the free parameters, then f); off by default. */
+void optimo_record_solve_trace(void* h, int enable);
+int optimo_solve_trace_size(void* h, int* rows, int* dim);
+int optimo_get_solve_trace(void* h, double* out);
+
 int optimo_cache_size(void* h, int* n_samples, int* dof); /* Core::GetOptimizationCache, core.h:134-144 */
 int optimo_get_cache(void* h, int which, double* out);    /* 0 time, 1 q, 2 q_dot, 3 q_ddot, 4 tau, 5 local_cost */
 void optimo_clear_optimization_cache(void* h);

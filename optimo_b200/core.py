@@ -93,6 +93,9 @@ _CORE_SIG = {
     "optimo_set_stop_optimization": (None, [_vp, ci]),
     "optimo_get_stop_optimization": (ci, [_vp]),
     "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
+    "optimo_record_solve_trace": (None, [_vp, ci]),
+    "optimo_solve_trace_size": (ci, [_vp, _ip, _ip]),
+    "optimo_get_solve_trace": (ci, [_vp, _dp]),
     "optimo_cache_size": (ci, [_vp, _ip, _ip]),
     "optimo_get_cache": (ci, [_vp, ci, _dp]),
     "optimo_clear_optimization_cache": (None, [_vp]),
@@ -487,6 +490,18 @@ class Core:
         v, n = C.c_double(0.0), C.c_int(0)
         self._ck(_core.optimo_perform_optimization(self.h, int(explicit_termination), C.byref(v), C.byref(n)))
         return v.value, n.value
+
+    def record_solve_trace(self, on=True):
+        _core.optimo_record_solve_trace(self.h, int(bool(on)))
+
+    def solve_trace(self):
+        """(X_free [rows, M], f [rows]) of every callback of the last recorded solve, in call order."""
+        rows, dim = C.c_int(0), C.c_int(0)
+        self._ck(_core.optimo_solve_trace_size(self.h, C.byref(rows), C.byref(dim)))
+        a = np.zeros((rows.value, dim.value + 1))
+        if a.size:
+            self._ck(_core.optimo_get_solve_trace(self.h, a.ctypes.data_as(_dp)))
+        return a[:, :-1].copy(), a[:, -1].copy()
 
     def GetOptimizationCache(self):
         n, dof = C.c_int(0), C.c_int(0)

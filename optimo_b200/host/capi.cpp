@@ -182,6 +182,19 @@ int optimo_perform_optimization(void* h, int explicit_termination, double* final
     });
 }
 
+void optimo_record_solve_trace(void* h, int enable) { C(h)->record_solve_trace_ = enable != 0; }
+int optimo_solve_trace_size(void* h, int* rows, int* dim)
+{
+    return guarded([&] {
+        *dim = C(h)->solve_trace_dim_;
+        *rows = *dim > 0 ? static_cast<int>(C(h)->solve_trace_.size()) / (*dim + 1) : 0;
+    });
+}
+int optimo_get_solve_trace(void* h, double* out)
+{
+    return guarded([&] { std::copy(C(h)->solve_trace_.begin(), C(h)->solve_trace_.end(), out); });
+}
+
 int optimo_cache_size(void* h, int* n_samples, int* dof)
 {
     return guarded([&] {

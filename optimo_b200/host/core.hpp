@@ -108,6 +108,11 @@ public:
     double last_solve_value_ = 0.0;
     int last_solve_evals_ = 0;
     std::string last_solve_status_;
+    /// Optional record of every callback of the last solve, in call order: M free parameters then f per row
+    /// (used to replay a solve against another implementation of the objective).
+    bool record_solve_trace_ = false;
+    int solve_trace_dim_ = 0;
+    std::vector<double> solve_trace_;
 
 private:
     void SyncEngine(double min_t, double max_t, const VecN& x_original);

@@ -102,6 +102,11 @@ double trampoline(unsigned n, const double* x, double* grad, void* p)
         t->xtmp.assign(x, x + n);
         if (grad) t->gradtmp.assign(n, 0.0); else t->gradtmp.clear();
         const double val = EvaluateObjective(t->xtmp, t->gradtmp, t->data);
+        Core* core = t->data->core;
+        if (core->record_solve_trace_) {
+            core->solve_trace_.insert(core->solve_trace_.end(), x, x + n);
+            core->solve_trace_.push_back(val);
+        }
         if (grad) std::copy(t->gradtmp.begin(), t->gradtmp.end(), grad);
         return val;
     } catch (const forced_stop&) {
@@ -158,6 +163,8 @@ void Core::PerformOptimization(bool explicit_termination)
 
     last_solve_evals_ = 0;
     last_solve_status_ = "";
+    solve_trace_.clear();
+    solve_trace_dim_ = static_cast<int>(M);
     if (M == 0) { object_->SetDescriptor(x_initial); last_solve_status_ = "no free dofs"; return; }
 
     // nloptutil::solve (nlopt-util.hpp:44-195)

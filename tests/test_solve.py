@@ -1,0 +1,86 @@
+"""BASELINE.json configs[1]: resources/scene-fox-tail.json, full NLopt (LN_BOBYQA) solve with the GPU objective
+callback -- Core::PerformOptimization (OptiMo/core_opt.cpp:60-157) over nloptutil::solve.
+
+Parity is by REPLAY: every x the solver asked the GPU callback about is re-evaluated
+by the CPU oracle and f must agree to 1e-9 relative; the end value is compared with an oracle-driven solve through
+the same NLopt build at 1e-6 relative (BOBYQA trajectories may fork on last-bit differences)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import nlopt_driver
+from conftest import GOLDEN, scene_path
+
+SOLVE_GOLDEN = os.path.join(GOLDEN, "solve_fox-tail.json")
+TAIL = ["tail_root", "tail_center"]
+needs_nlopt = pytest.mark.skipif(not nlopt_driver.available(), reason="third_party/_ref/libnlopt.so not built (make -C third_party)")
+
+
+def _oracle_solve(O):
+    orc = O.Oracle(scene_path("fox-tail"), "port")
+    orc.select_items(TAIL)
+    idx = orc.free_indices()
+    x_init, lower, upper = nlopt_driver.bounds_like_perform_optimization(orc.descriptor())
+    x_orig = orc.original()
+
+    def fun(xf):
+        full = x_init.copy()
+        full[idx] = xf
+        return orc.full_objective(full, x_orig)[0]
+
+    xs, fs, evals, trace = nlopt_driver.solve_bobyqa(fun, x_init[idx], lower[idx], upper[idx])
+    return orc, idx, x_init, xs, fs, evals, trace
+
+
+@needs_nlopt
+def test_oracle_driven_solve_matches_committed_golden(oracle_port):
+    """Pins the CPU side of the replay: same NLopt sources + same oracle => same trajectory as when the golden was made."""
+    orc, idx, x_init, xs, fs, evals, trace = _oracle_solve(oracle_port)
+    assert idx.size == 27
+    assert fs < trace[0][1] * 0.9          # it really minimised something
+    assert fs == min(f for _, f in trace)
+    with open(SOLVE_GOLDEN) as fh:
+        g = json.load(fh)
+    assert abs(trace[0][1] - g["f_initial"]) <= 1e-12 * abs(g["f_initial"])
+    assert abs(fs - g["f_final"]) <= 1e-6 * abs(g["f_final"])
+    assert abs(evals - g["evals"]) <= max(20, g["evals"] // 5)
+
+
+@pytest.mark.gpu
+@needs_nlopt
+def test_fox_tail_solve_replay_parity(oracle_port):
+    from optimo_b200.core import Core
+
+    c = Core(scene_path("fox-tail"))
+    c.select_items(TAIL)
+    x_before = c.GetDescriptor()
+    c.record_solve_trace(True)
+    f_final, evals = c.PerformOptimization(False)
+    X, F = c.solve_trace()
+    assert X.shape[1] == 27 and X.shape[0] == evals and evals > 50
+
+    orc = oracle_port.Oracle(scene_path("fox-tail"), "port")
+    orc.select_items(TAIL)
+    idx = orc.free_indices()
+    x_init, _, _ = nlopt_driver.bounds_like_perform_optimization(x_before)
+    x_orig = orc.original()
+    worst = 0.0
+    for xf, f in zip(X, F):
+        full = x_init.copy()
+        full[idx] = xf
+        fo = orc.full_objective(full, x_orig)[0]
+        worst = max(worst, abs(f - fo) / abs(fo))
+    assert worst <= 1e-9, worst
+
+    assert f_final == F.min()
+    with open(SOLVE_GOLDEN) as fh:
+        g = json.load(fh)
+    assert abs(F[0] - g["f_initial"]) <= 1e-9 * abs(g["f_initial"])
+    assert abs(f_final - g["f_final"]) <= 1e-6 * abs(g["f_final"]), (f_final, g["f_final"])
+    # the solve leaves x_opt in the scene (core_opt.cpp:156)
+    x_after = c.GetDescriptor()
+    assert np.array_equal(x_after[idx], X[np.argmin(F)])
+    frozen = np.setdiff1d(np.arange(x_after.size), idx)
+    assert np.array_equal(x_after[frozen], x_init[frozen])
