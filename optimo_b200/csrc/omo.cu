@@ -35,7 +35,8 @@ struct omo_ctx {
     std::vector<int> cp_of_pos, first_of_pos, last_of_pos, next_same;
     std::vector<double> joint_const_q;  // dynamics q of constant channels (for residues)
     int *d_cp_of_pos = nullptr, *d_first_of_pos = nullptr, *d_last_of_pos = nullptr, *d_next_same = nullptr;
-    int n_slots_nofk = 0, n_slots_fk = 0;
+    int n_slots_nofk[2] = {0, 0}, n_slots_fk[2] = {0, 0};   // [0] full tree, [1] pruned tree
+    std::vector<char> pruned;                                // [J] body left out of the pruned tree
 
     // window
     bool have_window = false;
@@ -166,29 +167,7 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         while (k >= 0) { if (k == sc->parent[j]) { ok = true; break; } k = sc->parent[k]; }
         if (!ok) return fail(ctx, OMO_BAD_ARG, "joints are not in DFS pre-order");
     }
-    // stack plan: (f, sincos) by depth for open non-leaf bodies; (v, a) and (L, t) by number of branching ancestors
-    int max_fs = 0, max_va = 0, max_fk = 0;
-    std::vector<int> nbranch_nonroot(J, 0), nbranch_all(J, 0);
-    for (int j = 0; j < J; ++j) {
-        S.parent[j] = sc->parent[j];
-        S.n_child[j] = (unsigned char)std::min(nchild[j], 255);
-        if (j > 0) {
-            const int p = sc->parent[j];
-            nbranch_nonroot[j] = nbranch_nonroot[p] + ((p > 0 && nchild[p] >= 2) ? 1 : 0);
-            nbranch_all[j] = nbranch_all[p] + ((nchild[p] >= 2) ? 1 : 0);
-        }
-        S.fs_slot[j] = -1; S.va_slot[j] = -1; S.fk_slot[j] = -1;
-        if (j > 0 && nchild[j] > 0) { S.fs_slot[j] = (short)(depth[j] - 1); max_fs = std::max(max_fs, depth[j]); }
-        if (j > 0 && nchild[j] >= 2) { S.va_slot[j] = (short)nbranch_nonroot[j]; max_va = std::max(max_va, nbranch_nonroot[j] + 1); }
-        if (nchild[j] >= 2) { S.fk_slot[j] = (short)nbranch_all[j]; max_fk = std::max(max_fk, nbranch_all[j] + 1); }
-    }
-    for (int j = 0; j < J; ++j) {
-        if (S.va_slot[j] >= 0) S.va_slot[j] = (short)(S.va_slot[j] + max_fs);
-        if (S.fk_slot[j] >= 0) S.fk_slot[j] = (short)(S.fk_slot[j] + max_fs + max_va);
-    }
-    ctx->n_slots_nofk = max_fs + max_va;
-    ctx->n_slots_fk = max_fs + max_va + max_fk;
-    S.n_slots = ctx->n_slots_fk;
+    for (int j = 0; j < J; ++j) { S.parent[j] = sc->parent[j]; S.n_child[j] = (unsigned char)std::min(nchild[j], 255); }
 
     // bodies (core_rbdl.cpp:228-252): body j hangs at Xtrans(parent.offset), carries j's own mass properties
     for (int j = 0; j < J; ++j) {
@@ -251,6 +230,7 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         }
         S.n_groups = g + 1;
         S.grp_begin[S.n_groups] = (short)n_list;
+        S.n_keyed = n_list;
         S.n_ex_rows = (S.n_groups > 1) ? 2 * G : G;
     }
 
@@ -271,6 +251,59 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         for (int i = 0; i <= nb; ++i) S.ik_joint[h][i] = path[i];
         S.ik_start[root] = (short)h;
         for (int i = 0; i < nb; ++i) { S.ik_of[path[i]] = (short)h; S.ik_idx[path[i]] = (short)i; S.ident[path[i]] = 0; }
+    }
+    // ---- walk plans -------------------------------------------------------------------------------------------
+    // Tree 0 = every body (used by the per-sample-output instance). Tree 1 = the bodies whose torque can depend on
+    // the candidate: a body is pruned when neither it, nor any ancestor, nor any descendant has a keyed or
+    // IK-driven angle -- its v, a, f are the same for every candidate (the stencil residue of constants at
+    // interior samples, exactly 0 at boundary samples), so the sum of its tau^2 is a per-scene constant
+    // (OmoDevScene::static_tsq, measured once from the full-tree instance in ensure_ready). A keyed root
+    // rotation moves every joint position (joint.cpp:64-83), so nothing is pruned then.
+    {
+        std::vector<char> dynamic(J, 0), anc_dyn(J, 0), sub_dyn(J, 0);
+        for (int j = 1; j < J; ++j) dynamic[j] = (S.dyn[j] != 0 || S.ik_of[j] >= 0) ? 1 : 0;
+        for (int j = 1; j < J; ++j) anc_dyn[j] = (char)(dynamic[j] | anc_dyn[sc->parent[j]]);
+        for (int j = J - 1; j >= 1; --j) { sub_dyn[j] |= dynamic[j]; sub_dyn[sc->parent[j]] |= sub_dyn[j]; }
+        ctx->pruned.assign(J, 0);
+        const bool allow_prune = (S.dyn[0] == 0) && std::getenv("OMO_NO_PRUNE") == nullptr;
+        for (int j = 1; j < J; ++j) ctx->pruned[j] = (allow_prune && !anc_dyn[j] && !sub_dyn[j]) ? 1 : 0;
+        for (int tree = 0; tree < 2; ++tree) {
+            std::vector<int> nch(J, 0), nb_nonroot(J, 0), nb_all(J, 0), fs(J, -1), va(J, -1), fk(J, -1);
+            auto keep = [&](int j) { return tree == 0 || !ctx->pruned[j]; };
+            for (int j = 1; j < J; ++j) if (keep(j)) nch[sc->parent[j]] += 1;
+            int max_fs = 0, max_va = 0, max_fk = 0, n_act = 0;
+            for (int j = 0; j < J; ++j) {
+                if (!keep(j)) continue;
+                if (j > 0) {
+                    const int pj = sc->parent[j];
+                    nb_nonroot[j] = nb_nonroot[pj] + ((pj > 0 && nch[pj] >= 2) ? 1 : 0);
+                    nb_all[j] = nb_all[pj] + ((nch[pj] >= 2) ? 1 : 0);
+                    S.act[tree][n_act++] = (unsigned char)j;
+                }
+                if (j > 0 && nch[j] > 0) { fs[j] = depth[j] - 1; max_fs = std::max(max_fs, depth[j]); }
+                if (j > 0 && nch[j] >= 2) { va[j] = nb_nonroot[j]; max_va = std::max(max_va, nb_nonroot[j] + 1); }
+                if (nch[j] >= 2) { fk[j] = nb_all[j]; max_fk = std::max(max_fk, nb_all[j] + 1); }
+            }
+            S.n_act[tree] = n_act;
+            for (int j = 0; j < J; ++j) {
+                if (va[j] >= 0) va[j] += max_fs;
+                if (fk[j] >= 0) fk[j] += max_fs + max_va;
+                auto byte = [](int v) { return v < 0 ? 0xff : (v & 0xff); };
+                if (max_fs + max_va + max_fk >= 0xff) return fail(ctx, OMO_BAD_ARG, "joint tree needs too many stack slots");
+                int4 w;
+                w.x = (j > 0 ? sc->parent[j] : 0) | (byte(fs[j]) << 8) | (byte(va[j]) << 16) | (byte(fk[j]) << 24);
+                w.y = (S.dyn[j] & 7) | ((S.ident[j] ? 1 : 0) << 3) | ((nch[j] > 0 ? 1 : 0) << 4) | (((S.grp_first[j] + 1) & 0xff) << 8) |
+                      (((S.ik_of[j] + 1) & 0xf) << 16) | ((S.ik_idx[j] & 0xf) << 20) | (((S.ik_start[j] + 1) & 0xf) << 24);
+                w.z = byte(S.chan_row[3 * j]) | (byte(S.chan_row[3 * j + 1]) << 8) | (byte(S.chan_row[3 * j + 2]) << 16);
+                w.w = 0;
+                S.meta[tree][j] = w;
+            }
+            S.n_slots_tree[tree] = max_fs + max_va + max_fk;
+            ctx->n_slots_nofk[tree] = max_fs + max_va;
+            ctx->n_slots_fk[tree] = max_fs + max_va + max_fk;
+        }
+        S.n_slots = ctx->n_slots_fk[0];
+        S.static_tsq = 0.0;
     }
     ctx->scene_dirty = true;
     omo_status st;
@@ -320,44 +353,37 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
 
 struct LaunchPlan { int ns, n_tiles, t_out; size_t smem; };
 
-size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns)
+size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns, bool out)
 {
-    const int slots = fk ? ctx->n_slots_fk : ctx->n_slots_nofk;
+    const int tree = out ? 0 : 1;
+    const int slots = fk ? ctx->n_slots_fk[tree] : ctx->n_slots_nofk[tree];
     const int ex_rows = ctx->hs.n_ex_rows + (ctx->n_ik > 0 ? 6 : 0);
     return std::max((size_t)(ex_rows + slots * OMO_SLOT) * ns * kBlockThreads * sizeof(double), (size_t)64 * sizeof(double));
 }
 
-// Tiling of the time axis: a block covers ns*128 consecutive samples of one candidate, 4 of them halo.
+// Tiling of the time axis: a block covers 128 consecutive samples of one candidate, 4 of them halo.
 LaunchPlan make_plan(const omo_ctx* ctx, int B, bool fk, bool ik, bool out)
 {
     LaunchPlan p;
-    p.ns = 1;
-    if (!ik && !out) {
-        const int t2 = 2 * kBlockThreads - 4;
-        const int tiles2 = (ctx->N_s + t2 - 1) / t2;
-        // two samples per thread pay off once the grid still fills the machine and two blocks fit one SM
-        const char* force = std::getenv("OMO_NS");   // tuning knob: 1 or 2 samples per thread
-        const bool want2 = force ? (std::atoi(force) == 2) : false;
-        if (want2 && smem_bytes(ctx, fk, 2) <= (size_t)113 * 1024 && (long long)B * tiles2 >= 2LL * ctx->sm_count * 2) p.ns = 2;
-    }
+    p.ns = 1;   // two samples per thread (NS = 2) measured slower on B200 (register pressure halves the resident warps)
     const int t_max = p.ns * kBlockThreads - 4;
     p.n_tiles = (ctx->N_s + t_max - 1) / t_max;
     p.t_out = (ctx->N_s + p.n_tiles - 1) / p.n_tiles;
-    p.smem = smem_bytes(ctx, fk, p.ns);
+    p.smem = smem_bytes(ctx, fk, p.ns, out);
     return p;
 }
 
-template <int NS, bool FK, bool IK, bool OUT>
+template <bool FK, bool IK, bool OUT, bool COUNT>
 omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B, const LaunchPlan& plan)
 {
     if (plan.smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
-    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<NS, FK, IK, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
+    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<1, FK, IK, OUT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing && !OUT) {
         OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
-    omo::objective_kernel<NS, FK, IK, OUT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
+    omo::objective_kernel<1, FK, IK, OUT, COUNT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
     OMO_CUDA(cudaGetLastError());
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1;
@@ -369,13 +395,14 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
 {
     const bool ik = ctx->n_ik > 0;
     if (ik || out) fk = true;
+    const bool count = P.counters != nullptr && !out;
     const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
     P.n_tiles = plan.n_tiles; P.T_out = plan.t_out;
     omo_status st;
-    if (out) st = ik ? launch_objective_t<1, true, true, true>(ctx, P, B, plan) : launch_objective_t<1, true, false, true>(ctx, P, B, plan);
-    else if (ik) st = launch_objective_t<1, true, true, false>(ctx, P, B, plan);
-    else if (plan.ns == 2) st = fk ? launch_objective_t<2, true, false, false>(ctx, P, B, plan) : launch_objective_t<2, false, false, false>(ctx, P, B, plan);
-    else st = fk ? launch_objective_t<1, true, false, false>(ctx, P, B, plan) : launch_objective_t<1, false, false, false>(ctx, P, B, plan);
+    if (out) st = ik ? launch_objective_t<true, true, true, false>(ctx, P, B, plan) : launch_objective_t<true, false, true, false>(ctx, P, B, plan);
+    else if (ik) st = count ? launch_objective_t<true, true, false, true>(ctx, P, B, plan) : launch_objective_t<true, true, false, false>(ctx, P, B, plan);
+    else if (fk) st = count ? launch_objective_t<true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false>(ctx, P, B, plan);
+    else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
     if (st != OMO_OK) return st;
     omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, d_f, d_terms);
     OMO_CUDA(cudaGetLastError());
@@ -459,7 +486,19 @@ omo_status ensure_ready(omo_ctx* ctx)
     if (ctx->p_orig_dirty) {
         // OriginalMotionCache (core_rbdl.cpp:357-368): positions of x_original, kept transposed [3J][N_s]
         if ((st = dev_alloc(ctx, &ctx->d_p_orig, (size_t)ctx->N_s * 3 * ctx->J)) != OMO_OK) return st;
+        ctx->hs.static_tsq = 0.0;
         if ((st = run_single_out(ctx, ctx->d_x0, false)) != OMO_OK) return st;
+        // candidate-independent share of sum tau^2: the pruned bodies' torques at an interior sample (full-tree run above)
+        if (ctx->N_s >= 5) {
+            std::vector<double> tau(3 * ctx->J);
+            OMO_CUDA(cudaMemcpyAsync(tau.data(), ctx->d_otau + (size_t)2 * 3 * ctx->J, tau.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+            OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+            double acc = 0.0;
+            for (int j = 1; j < ctx->J; ++j)
+                if (ctx->pruned[j]) for (int k = 0; k < 3; ++k) acc += tau[3 * j + k] * tau[3 * j + k];
+            ctx->hs.static_tsq = acc;
+        }
+        ctx->scene_dirty = true;
         const int n = ctx->N_s * 3 * ctx->J;
         omo::transpose_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_op, ctx->N_s, 3 * ctx->J, ctx->d_p_orig);
         OMO_CUDA(cudaGetLastError());

@@ -10,7 +10,8 @@
 // Template parameters: NS = time samples per thread (2 interleaves two independent dependency chains per
 // thread for the FP64 pipe and halves the per-body table / address overhead; 1 is the low-latency form for
 // small batches), FK = also run forward kinematics (positions; needed for D_traj and for IK), IK = scene has
-// IK chains, OUT = write the per-sample OptimizationCache arrays (single-candidate launches only).
+// IK chains, OUT = write the per-sample OptimizationCache arrays (single-candidate launches only; walks the FULL
+// tree, every other instance walks the pruned tree, see OmoDevScene::meta), COUNT = book executed curve / IK work.
 #ifndef OMO_OBJECTIVE_CUH
 #define OMO_OBJECTIVE_CUH
 
@@ -29,17 +30,40 @@ template <bool FK> struct Smp {
     bool owned, interior;
 };
 
-#define OMO_STK(slot, comp, j) stk[(((slot) * OMO_SLOT + (comp)) * NS + (j)) * NT + tid]
+#define OMO_NT 128  // threads per block (compile-time: every stack / exchange access gets an immediate offset)
+#define OMO_STK(slot, comp, j) stk[(((slot) * OMO_SLOT + (comp)) * NS + (j)) * OMO_NT + tid]
 
-template <int NS, bool FK, bool IK, bool OUT>
-__global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const OmoEvalParams P)
+struct BodyMeta {
+    int parent, fs, va, fk;   // slots: -1 = none
+    int dyn, grp, ik_of, ik_idx, ik_start;
+    bool ident, has_child;
+    int row[3];
+};
+
+__device__ __forceinline__ int meta_byte(const int w, const int sh) { const int v = (w >> sh) & 0xff; return v == 0xff ? -1 : v; }
+
+__device__ __forceinline__ BodyMeta load_meta(const int tree, const int b)
+{
+    const int4 w = c_scene.meta[tree][b];
+    BodyMeta M;
+    M.parent = w.x & 0xff; M.fs = meta_byte(w.x, 8); M.va = meta_byte(w.x, 16); M.fk = meta_byte(w.x, 24);
+    M.dyn = w.y & 7; M.ident = (w.y >> 3) & 1; M.has_child = (w.y >> 4) & 1;
+    M.grp = ((w.y >> 8) & 0xff) - 1; M.ik_of = ((w.y >> 16) & 0xf) - 1; M.ik_idx = (w.y >> 20) & 0xf; M.ik_start = ((w.y >> 24) & 0xf) - 1;
+    M.row[0] = w.z & 0xff; M.row[1] = (w.z >> 8) & 0xff; M.row[2] = (w.z >> 16) & 0xff;
+    return M;
+}
+
+template <int NS, bool FK, bool IK, bool OUT, bool COUNT>
+__global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(const OmoEvalParams P)
 {
     static_assert(!(IK && NS != 1), "IK scenes run one sample per thread");
     extern __shared__ double smem[];
+    __shared__ int s_seg0[3 * OMO_MAXJ];        // per keyed joint channel: points with time <= the block's first sample time
     const OmoDevScene& S = c_scene;
-    const int NT = blockDim.x;
+    constexpr int NT = OMO_NT;
+    constexpr int TREE = OUT ? 0 : 1;           // 0: every body, 1: candidate-independent subtrees pruned
     const int tid = threadIdx.x;
-    const int WIN = NS * NT;                    // samples in this block's window, halo included
+    constexpr int WIN = NS * NT;                // samples in this block's window, halo included
     const int cand = blockIdx.x / P.n_tiles;
     const int tile = blockIdx.x - cand * P.n_tiles;
     const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);
@@ -57,6 +81,22 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
     SV6 groot[OUT ? NS : 1];
     Smp<FK> sm[NS];
 
+    // ---- segment warm start: one binary search per keyed channel per block ---------------------------------------
+    if (sorted) {
+        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2, 0), N - 1));
+        for (int i = tid; i < S.n_keyed; i += NT) {
+            const int ch = S.grp_list[i];
+            const double* __restrict__ T = pc + S.chan_pos[ch];
+            int lo = 0, hi = S.chan_n[ch];
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (__ldg(T + mid) <= t_first) lo = mid + 1; else hi = mid;
+            }
+            s_seg0[i] = lo;
+        }
+    }
+    __syncthreads();
+
     // root state (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212): v = (0, qd), a = (0, qdd)
     auto set_root = [&](Smp<FK>& m) {
         m.v.w0 = m.v.w1 = m.v.w2 = 0.0; m.a.w0 = m.a.w1 = m.a.w2 = 0.0;
@@ -73,7 +113,8 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
         m.owned = (m.idx >= 2) && (s_raw < tile_end) && (s_raw >= 0);
         m.interior = (m.s >= 2) && (m.s <= N - 3);
         m.t = __ldg(P.tgrid + m.s);
-        m.tsq = 0.0; m.dtr = 0.0;
+        m.tsq = (!OUT && m.interior) ? S.static_tsq : 0.0;   // the pruned bodies' share (candidate-independent)
+        m.dtr = 0.0;
         set_root(m);
         m.f.w0 = m.f.w1 = m.f.w2 = m.f.l0 = m.f.l1 = m.f.l2 = 0.0;
         m.s0 = m.s1 = m.s2 = 0.0; m.c0 = m.c1 = m.c2 = 1.0;
@@ -108,40 +149,44 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
     }
 
     // tau = S^T f of body k from (f, sincos); returns g = X_lambda^T f and books |tau|^2
-    auto finalize = [&](const int k, Smp<FK>& m, const SV6& fk, const double s0, const double c0, const double s1, const double c1,
-                        const double s2, const double c2, SV6& g) {
+    auto finalize = [&](const int k, const bool idk, Smp<FK>& m, const SV6& fk, const double s0, const double c0, const double s1,
+                        const double c1, const double s2, const double c2, SV6& g) {
         double t0, t1, t2;
         const double r0 = S.body[k].r[0], r1 = S.body[k].r[1], r2 = S.body[k].r[2];
-        if (S.ident[k]) rnea_backward_identity(r0, r1, r2, fk, g, t0, t1, t2);
+        if (idk) rnea_backward_identity(r0, r1, r2, fk, g, t0, t1, t2);
         else rnea_backward(r0, r1, r2, s0, c0, s1, c1, s2, c2, fk, g, t0, t1, t2);
         m.tsq = fma(t0, t0, fma(t1, t1, fma(t2, t2, m.tsq)));
         if (OUT && m.owned) { P.o_tau[m.s * dof + 3 * k] = t0; P.o_tau[m.s * dof + 3 * k + 1] = t1; P.o_tau[m.s * dof + 3 * k + 2] = t2; }
     };
     // fold the finished leaf b_last and every finished ancestor back, stopping below `stop`
-    auto fold_back = [&](const int b_last, const int stop) {
+    auto fold_back = [&](const int b_last, const bool id_last, const int par_last, const int stop) {
         SV6 g[NS];
 #pragma unroll
-        for (int j = 0; j < NS; ++j) finalize(b_last, sm[j], sm[j].f, sm[j].s0, sm[j].c0, sm[j].s1, sm[j].c1, sm[j].s2, sm[j].c2, g[j]);
-        int k = S.parent[b_last];
+        for (int j = 0; j < NS; ++j)
+            finalize(b_last, id_last, sm[j], sm[j].f, sm[j].s0, sm[j].c0, sm[j].s1, sm[j].c1, sm[j].s2, sm[j].c2, g[j]);
+        int k = par_last;
 #pragma unroll 1
         while (k != stop) {
-            const int fs = S.fs_slot[k];
+            const int4 w = S.meta[TREE][k];
+            const bool idk = (w.y >> 3) & 1;
+            double* __restrict__ sp = stk + (size_t)((w.x >> 8) & 0xff) * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
                 SV6 fk;
-                fk.w0 = OMO_STK(fs, 0, j) + g[j].w0; fk.w1 = OMO_STK(fs, 1, j) + g[j].w1; fk.w2 = OMO_STK(fs, 2, j) + g[j].w2;
-                fk.l0 = OMO_STK(fs, 3, j) + g[j].l0; fk.l1 = OMO_STK(fs, 4, j) + g[j].l1; fk.l2 = OMO_STK(fs, 5, j) + g[j].l2;
-                finalize(k, sm[j], fk, OMO_STK(fs, 6, j), OMO_STK(fs, 7, j), OMO_STK(fs, 8, j), OMO_STK(fs, 9, j), OMO_STK(fs, 10, j),
-                         OMO_STK(fs, 11, j), g[j]);
+                fk.w0 = sp[(0 * NS + j) * NT] + g[j].w0; fk.w1 = sp[(1 * NS + j) * NT] + g[j].w1; fk.w2 = sp[(2 * NS + j) * NT] + g[j].w2;
+                fk.l0 = sp[(3 * NS + j) * NT] + g[j].l0; fk.l1 = sp[(4 * NS + j) * NT] + g[j].l1; fk.l2 = sp[(5 * NS + j) * NT] + g[j].l2;
+                if (idk) finalize(k, true, sm[j], fk, 0.0, 1.0, 0.0, 1.0, 0.0, 1.0, g[j]);
+                else finalize(k, false, sm[j], fk, sp[(6 * NS + j) * NT], sp[(7 * NS + j) * NT], sp[(8 * NS + j) * NT], sp[(9 * NS + j) * NT],
+                              sp[(10 * NS + j) * NT], sp[(11 * NS + j) * NT], g[j]);
             }
-            k = S.parent[k];
+            k = w.x & 0xff;
         }
         if (stop != 0) {
-            const int fs = S.fs_slot[stop];
+            double* __restrict__ sp = stk + (size_t)((S.meta[TREE][stop].x >> 8) & 0xff) * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
-                OMO_STK(fs, 0, j) += g[j].w0; OMO_STK(fs, 1, j) += g[j].w1; OMO_STK(fs, 2, j) += g[j].w2;
-                OMO_STK(fs, 3, j) += g[j].l0; OMO_STK(fs, 4, j) += g[j].l1; OMO_STK(fs, 5, j) += g[j].l2;
+                sp[(0 * NS + j) * NT] += g[j].w0; sp[(1 * NS + j) * NT] += g[j].w1; sp[(2 * NS + j) * NT] += g[j].w2;
+                sp[(3 * NS + j) * NT] += g[j].l0; sp[(4 * NS + j) * NT] += g[j].l1; sp[(5 * NS + j) * NT] += g[j].l2;
             }
         } else if (OUT) {
 #pragma unroll
@@ -153,79 +198,86 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
     };
 
     int xbuf = 0;
+    const int n_act = S.n_act[TREE];
+    BodyMeta Mp = load_meta(TREE, 0);   // the body visited last (starts at the root: fs = va = -1)
+    int bp = 0;
 #pragma unroll 1
-    for (int b = 1; b < J; ++b) {
-        const int par = S.parent[b];
-        // ---- leave body b-1: park it (descending) or fold the finished subtree(s) back --------------------
-        if (par == b - 1) {
-            const int fs = S.fs_slot[b - 1], va = S.va_slot[b - 1];
-            if (fs >= 0) {
-                const bool idp = S.ident[b - 1] != 0;
+    for (int ai = 0; ai < n_act; ++ai) {
+        const int b = S.act[TREE][ai];
+        const BodyMeta M = load_meta(TREE, b);
+        const int par = M.parent;
+        // ---- leave the previous body: park it (descending) or fold the finished subtree(s) back ----------------
+        {
+            if (par == bp) {
+                if (Mp.fs >= 0) {
+                    double* __restrict__ sp = stk + (size_t)Mp.fs * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
-                for (int j = 0; j < NS; ++j) {
-                    const Smp<FK>& m = sm[j];
-                    OMO_STK(fs, 0, j) = m.f.w0; OMO_STK(fs, 1, j) = m.f.w1; OMO_STK(fs, 2, j) = m.f.w2;
-                    OMO_STK(fs, 3, j) = m.f.l0; OMO_STK(fs, 4, j) = m.f.l1; OMO_STK(fs, 5, j) = m.f.l2;
-                    if (!idp) {
-                        OMO_STK(fs, 6, j) = m.s0; OMO_STK(fs, 7, j) = m.c0; OMO_STK(fs, 8, j) = m.s1;
-                        OMO_STK(fs, 9, j) = m.c1; OMO_STK(fs, 10, j) = m.s2; OMO_STK(fs, 11, j) = m.c2;
+                    for (int j = 0; j < NS; ++j) {
+                        const Smp<FK>& m = sm[j];
+                        sp[(0 * NS + j) * NT] = m.f.w0; sp[(1 * NS + j) * NT] = m.f.w1; sp[(2 * NS + j) * NT] = m.f.w2;
+                        sp[(3 * NS + j) * NT] = m.f.l0; sp[(4 * NS + j) * NT] = m.f.l1; sp[(5 * NS + j) * NT] = m.f.l2;
+                        if (!Mp.ident) {
+                            sp[(6 * NS + j) * NT] = m.s0; sp[(7 * NS + j) * NT] = m.c0; sp[(8 * NS + j) * NT] = m.s1;
+                            sp[(9 * NS + j) * NT] = m.c1; sp[(10 * NS + j) * NT] = m.s2; sp[(11 * NS + j) * NT] = m.c2;
+                        }
                     }
                 }
-            }
-            if (va >= 0) {
+                if (Mp.va >= 0) {
+                    double* __restrict__ sp = stk + (size_t)Mp.va * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
-                for (int j = 0; j < NS; ++j) {
-                    const Smp<FK>& m = sm[j];
-                    OMO_STK(va, 0, j) = m.v.w0; OMO_STK(va, 1, j) = m.v.w1; OMO_STK(va, 2, j) = m.v.w2;
-                    OMO_STK(va, 3, j) = m.v.l0; OMO_STK(va, 4, j) = m.v.l1; OMO_STK(va, 5, j) = m.v.l2;
-                    OMO_STK(va, 6, j) = m.a.w0; OMO_STK(va, 7, j) = m.a.w1; OMO_STK(va, 8, j) = m.a.w2;
-                    OMO_STK(va, 9, j) = m.a.l0; OMO_STK(va, 10, j) = m.a.l1; OMO_STK(va, 11, j) = m.a.l2;
+                    for (int j = 0; j < NS; ++j) {
+                        const Smp<FK>& m = sm[j];
+                        sp[(0 * NS + j) * NT] = m.v.w0; sp[(1 * NS + j) * NT] = m.v.w1; sp[(2 * NS + j) * NT] = m.v.w2;
+                        sp[(3 * NS + j) * NT] = m.v.l0; sp[(4 * NS + j) * NT] = m.v.l1; sp[(5 * NS + j) * NT] = m.v.l2;
+                        sp[(6 * NS + j) * NT] = m.a.w0; sp[(7 * NS + j) * NT] = m.a.w1; sp[(8 * NS + j) * NT] = m.a.w2;
+                        sp[(9 * NS + j) * NT] = m.a.l0; sp[(10 * NS + j) * NT] = m.a.l1; sp[(11 * NS + j) * NT] = m.a.l2;
+                    }
                 }
-            }
-            if (FK) {
-                const int fk = S.fk_slot[b - 1];
-                if (fk >= 0) {
+                if (FK && Mp.fk >= 0) {
+                    double* __restrict__ sp = stk + (size_t)Mp.fk * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
                     for (int j = 0; j < NS; ++j) {
 #pragma unroll
-                        for (int c = 0; c < 9; ++c) OMO_STK(fk, c, j) = sm[j].L[c];
+                        for (int c = 0; c < 9; ++c) sp[(c * NS + j) * NT] = sm[j].L[c];
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) OMO_STK(fk, 9 + c, j) = sm[j].W[c];
+                        for (int c = 0; c < 3; ++c) sp[((9 + c) * NS + j) * NT] = sm[j].W[c];
                     }
                 }
+            } else {
+                fold_back(bp, Mp.ident, Mp.parent, par);
             }
-        } else {
-            fold_back(b - 1, par);
+        }
+        if (par != bp) {
             // parent state for b (the root's is a function of the sample index only: recomputed, not parked)
             if (par == 0) {
 #pragma unroll
                 for (int j = 0; j < NS; ++j) set_root(sm[j]);
             } else {
-                const int va = S.va_slot[par];
+                const double* __restrict__ sp = stk + (size_t)((S.meta[TREE][par].x >> 16) & 0xff) * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
                 for (int j = 0; j < NS; ++j) {
                     Smp<FK>& m = sm[j];
-                    m.v.w0 = OMO_STK(va, 0, j); m.v.w1 = OMO_STK(va, 1, j); m.v.w2 = OMO_STK(va, 2, j);
-                    m.v.l0 = OMO_STK(va, 3, j); m.v.l1 = OMO_STK(va, 4, j); m.v.l2 = OMO_STK(va, 5, j);
-                    m.a.w0 = OMO_STK(va, 6, j); m.a.w1 = OMO_STK(va, 7, j); m.a.w2 = OMO_STK(va, 8, j);
-                    m.a.l0 = OMO_STK(va, 9, j); m.a.l1 = OMO_STK(va, 10, j); m.a.l2 = OMO_STK(va, 11, j);
+                    m.v.w0 = sp[(0 * NS + j) * NT]; m.v.w1 = sp[(1 * NS + j) * NT]; m.v.w2 = sp[(2 * NS + j) * NT];
+                    m.v.l0 = sp[(3 * NS + j) * NT]; m.v.l1 = sp[(4 * NS + j) * NT]; m.v.l2 = sp[(5 * NS + j) * NT];
+                    m.a.w0 = sp[(6 * NS + j) * NT]; m.a.w1 = sp[(7 * NS + j) * NT]; m.a.w2 = sp[(8 * NS + j) * NT];
+                    m.a.l0 = sp[(9 * NS + j) * NT]; m.a.l1 = sp[(10 * NS + j) * NT]; m.a.l2 = sp[(11 * NS + j) * NT];
                 }
             }
             if (FK) {
-                const int fk = S.fk_slot[par];
+                const double* __restrict__ sp = stk + (size_t)((S.meta[TREE][par].x >> 24) & 0xff) * (OMO_SLOT * NS * NT) + tid;
 #pragma unroll
                 for (int j = 0; j < NS; ++j) {
 #pragma unroll
-                    for (int c = 0; c < 9; ++c) sm[j].L[c] = OMO_STK(fk, c, j);
+                    for (int c = 0; c < 9; ++c) sm[j].L[c] = sp[(c * NS + j) * NT];
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) sm[j].W[c] = OMO_STK(fk, 9 + c, j);
+                    for (int c = 0; c < 3; ++c) sm[j].W[c] = sp[((9 + c) * NS + j) * NT];
                 }
             }
         }
 
         // ---- IK chains rooted here: solve once per sample (joint.cpp:38-44, ikhandler.cpp:103-164) ----------
         if (IK) {
-            const int h = S.ik_start[b];
+            const int h = M.ik_start;
             if (h >= 0) {
                 Smp<FK>& m = sm[0];
                 double tw[3];
@@ -246,62 +298,65 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
         }
 
         // ---- curve group starting here: sample its keyed channels for this thread's times (K-way interleaved) ----
-        {
-            const int g = S.grp_first[b];
-            if (g >= 0) {
-                const int g0 = S.grp_begin[g], g1 = S.grp_begin[g + 1];
+        if (M.grp >= 0) {
+            const int g0 = S.grp_begin[M.grp], g1 = S.grp_begin[M.grp + 1];
 #pragma unroll 1
-                for (int c0 = g0; c0 < g1; c0 += 3) {
-                    int pos[3], nn[3], row[3];
+            for (int c0 = g0; c0 < g1; c0 += 3) {
+                int pos[3], nn[3], row[3], sg[3];
 #pragma unroll
-                    for (int k = 0; k < 3; ++k) {
-                        const bool on = c0 + k < g1;
-                        const int ch = on ? S.grp_list[c0 + k] : 0;
-                        pos[k] = on ? S.chan_pos[ch] : 0; nn[k] = on ? S.chan_n[ch] : 0; row[k] = on ? S.chan_row[ch] : 0;
-                    }
-#pragma unroll
-                    for (int j = 0; j < NS; ++j) {
-                        double val[3];
-                        unsigned eb = 0, en = 0;
-                        eval_channels<3>(pc, P.n_cp, pos, nn, sm[j].t, sorted, val, eb, en);
-                        if (sm[j].owned) { n_bez += eb; n_newton += en; }   // halo samples repeat a neighbour tile's work
-#pragma unroll
-                        for (int k = 0; k < 3; ++k)
-                            if (nn[k] > 0) ex[row[k] * WIN + sm[j].idx] = val[k];
-                    }
+                for (int k = 0; k < 3; ++k) {
+                    const bool on = c0 + k < g1;
+                    const int ch = on ? S.grp_list[c0 + k] : 0;
+                    pos[k] = on ? S.chan_pos[ch] : 0; nn[k] = on ? S.chan_n[ch] : 0; row[k] = on ? S.chan_row[ch] : 0;
+                    sg[k] = on ? s_seg0[c0 + k] : 0;
                 }
-                __syncthreads();
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+                    double val[3];
+                    unsigned eb = 0, en = 0;
+                    eval_channels<3, COUNT>(pc, P.n_cp, pos, nn, sg, sm[j].t, sorted, val, eb, en);
+                    if (COUNT && sm[j].owned) { n_bez += eb; n_newton += en; }   // halo samples repeat a neighbour tile's work
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                        if (nn[k] > 0) ex[row[k] * WIN + sm[j].idx] = val[k];
+                }
             }
+            __syncthreads();
         }
 
-        // ---- angles of body b, their time derivatives, sin/cos ------------------------------------------------
-        const int dyn = S.dyn[b];
-        const int ikh = IK ? S.ik_of[b] : -1;
-        const bool ident = S.ident[b] != 0;
-        double q[NS][3], qd[NS][3], qdd[NS][3];
-        if (ident) {
+        // ---- forward dynamics step (v, a hold the parent's state on entry, the body's on exit) ------------------
+        const int ikh = IK ? M.ik_of : -1;
+        if (M.ident) {
+            // joint frozen at zero angles: E = I, qd = qdd = 0 exactly
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
+                Smp<FK>& m = sm[j];
+                if (OUT && m.owned) {
+                    const size_t o = m.s * dof + 3 * b;
 #pragma unroll
-                for (int k = 0; k < 3; ++k) { q[j][k] = 0.0; qd[j][k] = 0.0; qdd[j][k] = 0.0; }
-                sm[j].s0 = sm[j].s1 = sm[j].s2 = 0.0; sm[j].c0 = sm[j].c1 = sm[j].c2 = 1.0;
+                    for (int k = 0; k < 3; ++k) { P.o_q[o + k] = 0.0; P.o_qd[o + k] = 0.0; P.o_qdd[o + k] = 0.0; }
+                }
+                SV6 vn, an;
+                rnea_forward_identity(S.body[b], m.v, m.a, vn, an, m.f);
+                m.v = vn; m.a = an;
             }
         } else {
-            const int mask = (ikh >= 0) ? 7 : dyn;
-            double ss[NS][3], cc[NS][3];
+            // angles of body b, their time derivatives (core_rbdl.cpp:28-95), sin / cos
+            const int mask = (ikh >= 0) ? 7 : M.dyn;
+            double q[NS][3], qd[NS][3], qdd[NS][3], ss[NS][3], cc[NS][3];
             int rowk[3];
             if (IK && ikh >= 0) {
                 // IK-driven joint: its angles were solved per thread; exchange them through 3 dedicated double-buffered rows
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     rowk[k] = S.n_ex_rows + xbuf * 3 + k;
-                    ex[rowk[k] * WIN + sm[0].idx] = ikq[ikh * 3 * OMO_MAX_IK_CHAIN + 3 * S.ik_idx[b] + k];
+                    ex[rowk[k] * WIN + sm[0].idx] = ikq[ikh * 3 * OMO_MAX_IK_CHAIN + 3 * M.ik_idx + k];
                 }
                 __syncthreads();
                 xbuf ^= 1;
             } else {
 #pragma unroll
-                for (int k = 0; k < 3; ++k) rowk[k] = (mask >> k & 1) ? S.chan_row[3 * b + k] : 0;
+                for (int k = 0; k < 3; ++k) rowk[k] = M.row[k];
             }
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -342,35 +397,24 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
             }
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
-                sm[j].s0 = ss[j][0]; sm[j].s1 = ss[j][1]; sm[j].s2 = ss[j][2];
-                sm[j].c0 = cc[j][0]; sm[j].c1 = cc[j][1]; sm[j].c2 = cc[j][2];
+                Smp<FK>& m = sm[j];
+                m.s0 = ss[j][0]; m.s1 = ss[j][1]; m.s2 = ss[j][2];
+                m.c0 = cc[j][0]; m.c1 = cc[j][1]; m.c2 = cc[j][2];
+                if (OUT && m.owned) {
+                    const size_t o = m.s * dof + 3 * b;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) { P.o_q[o + k] = q[j][k]; P.o_qd[o + k] = qd[j][k]; P.o_qdd[o + k] = qdd[j][k]; }
+                }
+                SV6 vn, an;
+                rnea_forward(S.body[b], m.s0, m.c0, m.s1, m.c1, m.s2, m.c2, qd[j][0], qd[j][1], qd[j][2], qdd[j][0], qdd[j][1], qdd[j][2],
+                             m.v, m.a, vn, an, m.f);
+                m.v = vn; m.a = an;
             }
-        }
-        if (OUT) {
-#pragma unroll
-            for (int j = 0; j < NS; ++j) {
-                if (!sm[j].owned) continue;
-                const size_t o = sm[j].s * dof + 3 * b;
-#pragma unroll
-                for (int k = 0; k < 3; ++k) { P.o_q[o + k] = q[j][k]; P.o_qd[o + k] = qd[j][k]; P.o_qdd[o + k] = qdd[j][k]; }
-            }
-        }
-
-        // ---- forward dynamics step (v, a hold the parent's state on entry, the body's on exit) ------------------
-#pragma unroll
-        for (int j = 0; j < NS; ++j) {
-            Smp<FK>& m = sm[j];
-            SV6 vn, an;
-            if (ident) rnea_forward_identity(S.body[b], m.v, m.a, vn, an, m.f);
-            else rnea_forward(S.body[b], m.s0, m.c0, m.s1, m.c1, m.s2, m.c2, qd[j][0], qd[j][1], qd[j][2], qdd[j][0], qdd[j][1], qdd[j][2],
-                              m.v, m.a, vn, an, m.f);
-            m.v = vn; m.a = an;
         }
 
         // ---- forward kinematics: p_b and the world affine handed to b's children ----------------------------------
         if (FK) {
             const double o0 = S.offset[b][0], o1 = S.offset[b][1], o2 = S.offset[b][2];
-            const bool has_child = S.n_child[b] > 0;
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
                 Smp<FK>& m = sm[j];
@@ -383,8 +427,8 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
                     m.dtr += d0 * d0 + d1 * d1 + d2 * d2;
                 }
                 if (OUT && m.owned && P.o_p) { P.o_p[m.s * dof + 3 * b] = p0; P.o_p[m.s * dof + 3 * b + 1] = p1; P.o_p[m.s * dof + 3 * b + 2] = p2; }
-                if (has_child) {
-                    if (!ident) {
+                if (M.has_child) {
+                    if (!M.ident) {
                         // L <- L * Rz(q2) Ry(q1) Rx(q0)
                         const double s0 = m.s0, c0 = m.c0, s1 = m.s1, c1 = m.c1, s2 = m.s2, c2 = m.c2;
                         const double R00 = c2 * c1, R01 = c2 * s1 * s0 - s2 * c0, R02 = c2 * s1 * c0 + s2 * s0;
@@ -404,10 +448,11 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
                 }
             }
         }
+        Mp = M; bp = b;
     }
 
     // ---- fold everything that is still open back to the root ------------------------------------------------------
-    if (J > 1) fold_back(J - 1, 0);
+    if (n_act > 0) fold_back(bp, Mp.ident, Mp.parent, 0);
 
     // ---- cost of the samples and block reduction (local_cost = |tau[3:]|^2 dt, core_rbdl.cpp:331-334) ---------------
     double wc = 0.0, wt = 0.0;
@@ -440,7 +485,7 @@ __global__ void __launch_bounds__(128, (NS == 1 ? 4 : 2)) objective_kernel(const
         P.partial[(size_t)blockIdx.x * 2] = C;
         P.partial[(size_t)blockIdx.x * 2 + 1] = D;
     }
-    if (P.counters) {
+    if (COUNT && P.counters) {
         unsigned cb = n_bez, cn = n_newton, ci = n_iksolve, cj = n_ikiter;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {

@@ -37,6 +37,19 @@ struct OmoDevScene {
     unsigned char n_child[OMO_MAXJ];
     unsigned char dyn[OMO_MAXJ];  // bit a: channel 3j+a is keyframed
     unsigned char ident[OMO_MAXJ];  // 1: all three angles are the constant 0 and the joint is not IK-driven (E = I, qd = qdd = 0)
+    // Packed per-body walk metadata, one 16-byte uniform load per body (index 0: full tree, 1: pruned tree):
+    //   x = parent | fs_slot << 8 | va_slot << 16 | fk_slot << 24                  (0xFF = none)
+    //   y = dyn (bits 0-2) | ident (3) | has_child (4) | (grp_first + 1) << 8 | (ik_of + 1) << 16 | ik_idx << 20 | (ik_start + 1) << 24
+    //   z = chan_row[3b] | chan_row[3b+1] << 8 | chan_row[3b+2] << 16                (0xFF = none)
+    // The pruned tree leaves out every body whose whole subtree AND whole ancestor chain are constant (no keyed
+    // channel, no IK): their torques do not depend on the candidate (see omo.cu, static_tsq).
+    int4 meta[2][OMO_MAXJ];
+    unsigned char act[2][OMO_MAXJ];   // bodies >= 1 visited by the walk, DFS order
+    int n_act[2];
+    int n_slots_tree[2];
+    int n_keyed;                      // entries of grp_list
+    int pad1;
+    double static_tsq;                // sum of tau^2 of the pruned bodies at an interior sample (0 at boundary samples)
     short grp_first[OMO_MAXJ];        // group that starts at this body, -1 if none
     short grp_begin[OMO_MAXJ + 1];    // group g owns grp_list[grp_begin[g] .. grp_begin[g+1])
     short grp_list[3 * OMO_MAXJ];     // keyed joint channels (3*j + axis, j >= 1) in body order

@@ -2,8 +2,8 @@
 callback -- Core::PerformOptimization (OptiMo/core_opt.cpp:60-157) over nloptutil::solve.
 
 Parity is by REPLAY: every x the solver asked the GPU callback about is re-evaluated
-by the CPU oracle and f must agree to 1e-9 relative; the end value is compared with an oracle-driven solve through
-the same NLopt build at 1e-6 relative (BOBYQA trajectories may fork on last-bit differences)."""
+by the CPU oracle and f must agree to 1e-9 relative; the end value is compared loosely with an oracle-driven solve
+through the same NLopt build (BOBYQA trajectories fork on last-bit differences and both stop at the maxeval cap)."""
 import json
 import os
 
@@ -78,7 +78,11 @@ def test_fox_tail_solve_replay_parity(oracle_port):
     with open(SOLVE_GOLDEN) as fh:
         g = json.load(fh)
     assert abs(F[0] - g["f_initial"]) <= 1e-9 * abs(g["f_initial"])
-    assert abs(f_final - g["f_final"]) <= 1e-6 * abs(g["f_final"]), (f_final, g["f_final"])
+    # End value: both solves stop at the maxeval = 2000 cap (core_opt.cpp:132) still descending, and BOBYQA's path forks
+    # on last-bit differences of f (measured: 2669.40 GPU-driven vs 2693.38 oracle-driven from 26566.8), so the
+    # end values agree only loosely; the per-evaluation replay above is the parity statement.
+    assert f_final < 0.15 * F[0]
+    assert abs(f_final - g["f_final"]) <= 0.05 * abs(g["f_final"]), (f_final, g["f_final"])
     # the solve leaves x_opt in the scene (core_opt.cpp:156)
     x_after = c.GetDescriptor()
     assert np.array_equal(x_after[idx], X[np.argmin(F)])
