@@ -248,7 +248,12 @@ def run_ours(args):
     eng.set_counting(False)
     n_se = B * N_s
     bez, newt = cnt["bezier_evals"] / n_se, cnt["newton_iters"] / n_se
-    flops_se = synthetic.flops_per_sample_eval(J, bez, newt)
+    # SURVEY.md section 8(d) formula. `flops_reference_work` counts all J-1 bodies (what the reference executes per
+    # sample); `flops_executed` counts only the bodies the batch kernel walks (candidate-independent subtrees are
+    # evaluated once per window, SURVEY.md Appendix B: "must then report executed FLOPs") -- `frac` uses the latter.
+    walked, walked_general = eng.walked_bodies()
+    flops_ref = synthetic.flops_per_sample_eval(J, bez, newt)
+    flops_se = synthetic.flops_per_sample_eval(walked + 1, bez, newt)
     dfma_peak = eng.dfma_peak()                                  # measured in this run: MEASURED_PEAKS.json has no FP64 figure
     k_ms_per_launch = k_ms / max(k_n, 1)
     achieved = n_se * flops_se / (k_ms_per_launch * 1e-3)
@@ -260,12 +265,21 @@ def run_ours(args):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     alg_bytes = 8.0 * (B * 6 * (D // 5) + 2 * B * ((N_s + 123) // 124))   # prepared control points in, tile partials out
+    traffic = None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed `ncu --set full` capture
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            traffic = json.load(fh).get(args.workload, {}).get("dram_bytes_per_launch")
+    except Exception:
+        pass
     roofline = {
         "bound": "fp64", "achieved": achieved / 1e12, "peak": dfma_peak / 1e12, "unit": "TFLOP/s", "frac": achieved / dfma_peak,
-        "traffic": None, "kernel": "omo::objective_kernel", "kernel_ms": k_ms_per_launch, "kernel_share_of_step": k_ms_per_launch / ms_dev,
-        "flops_per_sample_eval": flops_se, "bezier_evals_per_sample_eval": bez, "newton_iters_per_sample_eval": newt,
+        "traffic": traffic, "kernel": "omo::objective_kernel", "kernel_ms": k_ms_per_launch, "kernel_share_of_step": k_ms_per_launch / ms_dev,
+        "flops_per_sample_eval": flops_se, "flops_per_sample_eval_reference_work": flops_ref,
+        "frac_of_reference_work": n_se * flops_ref / (k_ms_per_launch * 1e-3) / dfma_peak,
+        "bodies": {"scene": J - 1, "walked": walked, "walked_general": walked_general},
+        "bezier_evals_per_sample_eval": bez, "newton_iters_per_sample_eval": newt,
         "peak_source": "dependent-free DFMA microbenchmark (omo_measure_dfma_peak) in this run",
-        "hbm": {"algorithmic_GBps": alg_bytes / (k_ms_per_launch * 1e-3) / 1e9, "peak_GBps": hbm_peak,
+        "hbm": {"algorithmic_bytes": alg_bytes, "algorithmic_GBps": alg_bytes / (k_ms_per_launch * 1e-3) / 1e9, "peak_GBps": hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
     }
 
@@ -273,7 +287,7 @@ def run_ours(args):
     from oracle import oracle as O
     cores = os.cpu_count() or 1
     sample = max(cores, min(B, 64 * cores))
-    if args.workload == "grad":
+    if args.workload == "grad" or world > 1:
         cpu = None
     else:
         leg = cpu_reference_leg(scene, sample, 0, x0)

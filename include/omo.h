@@ -107,6 +107,11 @@ omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D);
 int omo_num_samples(const omo_ctx* ctx);  /* N_s */
 int omo_descriptor_size(const omo_ctx* ctx); /* D */
 int omo_dof(const omo_ctx* ctx);          /* 3*J */
+/* Bodies the batch kernels actually run per sample-eval: bodies whose torque cannot depend on the candidate (no
+ * keyed / IK-driven angle on the body, its ancestors or its descendants) are evaluated once per window instead.
+ * general_out (optional): how many of the walked bodies take the general EulerXYZ step (the rest are joints
+ * frozen at zero angles, E = I). Used to report EXECUTED FLOPs. */
+int omo_num_walked_bodies(const omo_ctx* ctx, int* general_out);
 omo_status omo_get_time_grid(const omo_ctx* ctx, double* t_out /* [N_s] */);
 omo_status omo_get_cost_weights(const omo_ctx* ctx, double* w_out /* [N_s] */);
 omo_status omo_get_p_original(omo_ctx* ctx, double* p_out /* [N_s * 3J], sample-major */);

@@ -112,6 +112,7 @@ _OMO_SIG = {
     "omo_num_samples": (ci, [_vp]),
     "omo_descriptor_size": (ci, [_vp]),
     "omo_dof": (ci, [_vp]),
+    "omo_num_walked_bodies": (ci, [_vp, _ip]),
     "omo_get_time_grid": (ci, [_vp, _dp]),
     "omo_get_cost_weights": (ci, [_vp, _dp]),
     "omo_get_p_original": (ci, [_vp, _dp]),
@@ -186,6 +187,12 @@ class Engine:
     @property
     def dof(self):
         return _omo.omo_dof(self.h)
+
+    def walked_bodies(self):
+        """(bodies the batch kernels run per sample-eval, how many of them take the general EulerXYZ step)."""
+        g = C.c_int(0)
+        n = _omo.omo_num_walked_bodies(self.h, C.byref(g))
+        return n, g.value
 
     def time_grid(self):
         t = np.zeros(self.num_samples)

@@ -183,6 +183,7 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
     for (int ch = 0; ch < sc->n_channels; ++ch) {
         const int n = sc->chan_n_cp[ch], first = sc->chan_first_cp[ch];
         if (n < 0 || (n > 0 && (first < 0 || first + n > sc->n_cp))) return fail(ctx, OMO_BAD_ARG, "bad channel control-point range");
+        if (n > 65535) return fail(ctx, OMO_BAD_ARG, "more than 65535 control points on one channel");
         int cpos = -1;
         if (n > 0) {
             if (first != pos) return fail(ctx, OMO_BAD_ARG, "channels must list their control points contiguously in descriptor order");
@@ -299,6 +300,7 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
                 S.meta[tree][j] = w;
             }
             S.n_slots_tree[tree] = max_fs + max_va + max_fk;
+            S.n_slots_nofk_tree[tree] = max_fs + max_va;
             ctx->n_slots_nofk[tree] = max_fs + max_va;
             ctx->n_slots_fk[tree] = max_fs + max_va + max_fk;
         }
@@ -358,7 +360,8 @@ size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns, bool out)
     const int tree = out ? 0 : 1;
     const int slots = fk ? ctx->n_slots_fk[tree] : ctx->n_slots_nofk[tree];
     const int ex_rows = ctx->hs.n_ex_rows + (ctx->n_ik > 0 ? 6 : 0);
-    return std::max((size_t)(ex_rows + slots * OMO_SLOT) * ns * kBlockThreads * sizeof(double), (size_t)64 * sizeof(double));
+    const size_t seg = (((size_t)(kBlockThreads / 32) * ctx->hs.n_keyed * sizeof(unsigned short)) + 15) & ~(size_t)15;
+    return std::max((size_t)(ex_rows + slots * OMO_SLOT) * ns * kBlockThreads * sizeof(double) + seg, (size_t)64 * sizeof(double));
 }
 
 // Tiling of the time axis: a block covers 128 consecutive samples of one candidate, 4 of them halo.
@@ -642,6 +645,14 @@ omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D)
 int omo_num_samples(const omo_ctx* ctx) { return ctx ? ctx->N_s : 0; }
 int omo_descriptor_size(const omo_ctx* ctx) { return ctx ? ctx->D : 0; }
 int omo_dof(const omo_ctx* ctx) { return ctx ? 3 * ctx->J : 0; }
+int omo_num_walked_bodies(const omo_ctx* ctx, int* general_out)
+{
+    if (!ctx) return 0;
+    int gen = 0;
+    for (int i = 0; i < ctx->hs.n_act[1]; ++i) gen += ctx->hs.ident[ctx->hs.act[1][i]] ? 0 : 1;
+    if (general_out) *general_out = gen;
+    return ctx->hs.n_act[1];
+}
 
 omo_status omo_get_time_grid(const omo_ctx* ctx, double* t_out)
 {

@@ -58,7 +58,6 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
 {
     static_assert(!(IK && NS != 1), "IK scenes run one sample per thread");
     extern __shared__ double smem[];
-    __shared__ int s_seg0[3 * OMO_MAXJ];        // per keyed joint channel: points with time <= the block's first sample time
     const OmoDevScene& S = c_scene;
     constexpr int NT = OMO_NT;
     constexpr int TREE = OUT ? 0 : 1;           // 0: every body, 1: candidate-independent subtrees pruned
@@ -81,10 +80,14 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
     SV6 groot[OUT ? NS : 1];
     Smp<FK> sm[NS];
 
-    // ---- segment warm start: one binary search per keyed channel per block ---------------------------------------
+    // ---- segment warm start: one binary search per keyed channel per WARP (for the time of its first lane; the
+    // lanes' times ascend), so each thread later only walks the few keys its own time lies beyond ---------------
+    // seg0[warp][n_keyed] (16-bit) sits behind the stack in dynamic shared memory
+    unsigned short* __restrict__ seg0 =
+        reinterpret_cast<unsigned short*>(stk + (size_t)(FK ? S.n_slots_tree[TREE] : S.n_slots_nofk_tree[TREE]) * (OMO_SLOT * NS * NT)) + (tid >> 5) * S.n_keyed;
     if (sorted) {
-        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2, 0), N - 1));
-        for (int i = tid; i < S.n_keyed; i += NT) {
+        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2 + (tid & ~31), 0), N - 1));
+        for (int i = tid & 31; i < S.n_keyed; i += 32) {
             const int ch = S.grp_list[i];
             const double* __restrict__ T = pc + S.chan_pos[ch];
             int lo = 0, hi = S.chan_n[ch];
@@ -92,10 +95,10 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
                 const int mid = (lo + hi) >> 1;
                 if (__ldg(T + mid) <= t_first) lo = mid + 1; else hi = mid;
             }
-            s_seg0[i] = lo;
+            seg0[i] = (unsigned short)lo;
         }
     }
-    __syncthreads();
+    __syncwarp();
 
     // root state (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212): v = (0, qd), a = (0, qdd)
     auto set_root = [&](Smp<FK>& m) {
@@ -134,7 +137,7 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
                 e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], m.t, sorted, n_bez, n_newton)
                                            : S.chan_const[k];
             double sx, cx, sy, cy, sz, cz;
-            sincos(e[0], &sx, &cx); sincos(e[1], &sy, &cy); sincos(e[2], &sz, &cz);
+            sincos_angle(e[0], &sx, &cx); sincos_angle(e[1], &sy, &cy); sincos_angle(e[2], &sz, &cz);
             m.L[0] = cz * cy; m.L[1] = cz * sy * sx - sz * cx; m.L[2] = cz * sy * cx + sz * sx;
             m.L[3] = sz * cy; m.L[4] = sz * sy * sx + cz * cx; m.L[5] = sz * sy * cx - cz * sx;
             m.L[6] = -sy;     m.L[7] = cy * sx;                m.L[8] = cy * cx;
@@ -308,7 +311,7 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
                     const bool on = c0 + k < g1;
                     const int ch = on ? S.grp_list[c0 + k] : 0;
                     pos[k] = on ? S.chan_pos[ch] : 0; nn[k] = on ? S.chan_n[ch] : 0; row[k] = on ? S.chan_row[ch] : 0;
-                    sg[k] = on ? s_seg0[c0 + k] : 0;
+                    sg[k] = on ? seg0[c0 + k] : 0;
                 }
 #pragma unroll
                 for (int j = 0; j < NS; ++j) {
@@ -382,7 +385,7 @@ __global__ void __launch_bounds__(OMO_NT, (NS == 1 ? 4 : 2)) objective_kernel(co
                             qd[j][k] = (p1 - m1) * P.inv_2dt;
                             qdd[j][k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
                         }
-                        sincos(x, &ss[j][k], &cc[j][k]);
+                        sincos_angle(x, &ss[j][k], &cc[j][k]);
                     }
                 } else {
                     const double qc = S.chan_const[3 * b + k], sc_ = S.chan_sin[3 * b + k], cc_ = S.chan_cos[3 * b + k];

@@ -46,7 +46,8 @@ struct OmoDevScene {
     int4 meta[2][OMO_MAXJ];
     unsigned char act[2][OMO_MAXJ];   // bodies >= 1 visited by the walk, DFS order
     int n_act[2];
-    int n_slots_tree[2];
+    int n_slots_tree[2];        // stack slots with the FK slots
+    int n_slots_nofk_tree[2];   // and without
     int n_keyed;                      // entries of grp_list
     int pad1;
     double static_tsq;                // sum of tau^2 of the pruned bodies at an interior sample (0 at boundary samples)
