@@ -168,6 +168,16 @@ omo_status omo_get_counters(omo_ctx* ctx, unsigned long long* out5);
 /* Timing of the main objective kernel: accumulates CUDA-event time of every launch between reset and read. */
 omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* launches);
 
+/* Scene-specialised kernels (optimo_b200/csrc/omo_jit.hpp): for launches of >= 64 K sample-evals the engine unrolls
+ * the tree walk of its scene into straight-line CUDA (the same device code as the table-driven kernel), compiles it
+ * for sm_100a with NVRTC and launches that. OMO_JIT=0 disables it, OMO_JIT=1 makes it mandatory for every launch.
+ * omo_jit_info: out4[0] launches that went through a specialised kernel, [1] instances compiled, [2] their largest
+ * register count, [3] total compile time in ms; log = why specialisation was not possible, if it was not.
+ * omo_jit_probe (host only, needs no GPU): generates and compiles the specialised kernel of `scene`; writes
+ * <dump_prefix>.cu / .cubin when dump_prefix is not NULL. */
+omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int log_cap);
+omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const char* dump_prefix, char* log, int log_cap);
+
 /* Sustained dependent-free DFMA throughput of the device in FLOP/s (roofline denominator; runs ~ms). */
 omo_status omo_measure_dfma_peak(omo_ctx* ctx, double* flops_per_s);
 

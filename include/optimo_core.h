@@ -71,6 +71,10 @@ void optimo_set_stop_optimization(void* h, int flag);     /* Core::stop_optimiza
 int optimo_get_stop_optimization(void* h);
 int optimo_perform_optimization(void* h, int explicit_termination, double* final_value, int* evals);  /* core_opt.cpp:60-157 */
 
+/* Host-only (no GPU): generate + NVRTC-compile the scene-specialised objective kernel of the current scene
+ * (include/omo.h: omo_jit_probe). Returns 0 when it compiled; `log` = stack placement summary and compiler log. */
+int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump_prefix, char* log, int cap);
+
 /* Record of the last solve's callbacks in call order (rows x (dim + 1): the free parameters, then f); off by default. */
 void optimo_record_solve_trace(void* h, int enable);
 int optimo_solve_trace_size(void* h, int* rows, int* dim);

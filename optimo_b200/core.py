@@ -93,6 +93,7 @@ _CORE_SIG = {
     "optimo_set_stop_optimization": (None, [_vp, ci]),
     "optimo_get_stop_optimization": (ci, [_vp]),
     "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
+    "optimo_probe_specialised_kernel": (ci, [_vp, ci, ci, cs, cs, ci]),
     "optimo_record_solve_trace": (None, [_vp, ci]),
     "optimo_solve_trace_size": (ci, [_vp, _ip, _ip]),
     "optimo_get_solve_trace": (ci, [_vp, _dp]),
@@ -134,6 +135,7 @@ _OMO_SIG = {
     "omo_get_counters": (ci, [_vp, C.POINTER(_ull)]),
     "omo_kernel_timing": (ci, [_vp, ci, _dp, _ip]),
     "omo_measure_dfma_peak": (ci, [_vp, _dp]),
+    "omo_jit_info": (ci, [_vp, C.POINTER(_ull), cs, ci]),
 }
 for _n, (_r, _a) in _OMO_SIG.items():
     _sig(_omo, _n, _r, _a)
@@ -287,6 +289,13 @@ class Engine:
         ms, n = C.c_double(0.0), C.c_int(0)
         self._ck(_omo.omo_kernel_timing(self.h, int(reset), C.byref(ms), C.byref(n)), "omo_kernel_timing")
         return ms.value, n.value
+
+    def jit_info(self):
+        out = (_ull * 4)()
+        buf = C.create_string_buffer(1 << 14)
+        self._ck(_omo.omo_jit_info(self.h, out, buf, len(buf)), "omo_jit_info")
+        return {"launches": int(out[0]), "instances": int(out[1]), "max_registers": int(out[2]), "compile_ms": int(out[3]),
+                "log": buf.value.decode(errors="replace")}
 
     def dfma_peak(self):
         v = C.c_double(0.0)
@@ -497,6 +506,12 @@ class Core:
         v, n = C.c_double(0.0), C.c_int(0)
         self._ck(_core.optimo_perform_optimization(self.h, int(explicit_termination), C.byref(v), C.byref(n)))
         return v.value, n.value
+
+    def probe_specialised_kernel(self, fk=False, count=False, dump_prefix=None):
+        """Host-only: generates and NVRTC-compiles the scene-specialised kernel; returns (ok, log)."""
+        buf = C.create_string_buffer(1 << 16)
+        rc = _core.optimo_probe_specialised_kernel(self.h, int(fk), int(count), dump_prefix.encode() if dump_prefix else None, buf, len(buf))
+        return rc == 0, buf.value.decode(errors="replace")
 
     def record_solve_trace(self, on=True):
         _core.optimo_record_solve_trace(self.h, int(bool(on)))

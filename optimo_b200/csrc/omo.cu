@@ -12,6 +12,13 @@
 
 #include "omo_objective.cuh"
 
+#include <chrono>
+
+#include "omo_jit.hpp"
+#include "omo_jit_sources.inc"
+
+static_assert(OMO_MAX_JOINTS == 128 && OMO_MAX_IK == 8 && OMO_MAX_IK_CHAIN == 8, "keep the NVRTC branch of omo_scene.cuh in sync with include/omo.h");
+
 namespace {
 
 std::string g_create_error;
@@ -37,6 +44,23 @@ struct omo_ctx {
     int *d_cp_of_pos = nullptr, *d_first_of_pos = nullptr, *d_last_of_pos = nullptr, *d_next_same = nullptr;
     int n_slots_nofk[2] = {0, 0}, n_slots_fk[2] = {0, 0};   // [0] full tree, [1] pruned tree
     std::vector<char> pruned;                                // [J] body left out of the pruned tree
+    unsigned long long scene_version = 1;                    // bumped whenever hs changes
+
+    // scene-specialised kernels (omo_jit.hpp), one per (fk, ik, count) instance
+    struct JitKernel {
+        bool tried = false, ok = false;
+        omo_jit::CUmodule mod = nullptr;
+        omo_jit::CUfunction fn = nullptr;
+        omo_jit::CUdeviceptr d_scene = 0;
+        size_t smem = 0;
+        int regs = 0;
+        unsigned long long uploaded_version = 0;
+        double compile_ms = 0.0;
+    };
+    JitKernel jit[8];
+    int jit_mode = -1;            // -1: auto (large launches), 0: never, 1: always (OMO_JIT)
+    std::string jit_log;
+    unsigned long long jit_launches = 0;
 
     // window
     bool have_window = false;
@@ -139,7 +163,8 @@ void constant_residue(double c, double dx, double* qd, double* qdd)
     *qdd = (-v + 16.0 * v - 30.0 * v + 16.0 * v - v) / (12.0 * dx * dx);
 }
 
-omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
+// Host-only part of omo_create: flattens the scene into OmoDevScene and the prepare tables (no CUDA calls).
+omo_status build_tables(omo_ctx* ctx, const omo_scene_desc* sc)
 {
     const int J = sc->n_joints;
     if (J < 1 || J > OMO_MAXJ) return fail(ctx, OMO_BAD_ARG, "n_joints must be in [1, OMO_MAX_JOINTS]");
@@ -308,7 +333,14 @@ omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
         S.static_tsq = 0.0;
     }
     ctx->scene_dirty = true;
-    omo_status st;
+    ctx->scene_version += 1;
+    return OMO_OK;
+}
+
+omo_status build_scene(omo_ctx* ctx, const omo_scene_desc* sc)
+{
+    omo_status st = build_tables(ctx, sc);
+    if (st != OMO_OK) return st;
     if ((st = upload(ctx, &ctx->d_cp_of_pos, ctx->cp_of_pos)) != OMO_OK) return st;
     if ((st = upload(ctx, &ctx->d_first_of_pos, ctx->first_of_pos)) != OMO_OK) return st;
     if ((st = upload(ctx, &ctx->d_last_of_pos, ctx->last_of_pos)) != OMO_OK) return st;
@@ -322,6 +354,7 @@ void refresh_residues(omo_ctx* ctx)
     for (int ch = 0; ch < 3 * ctx->J; ++ch) constant_residue(S.chan_const[ch], ctx->dt, &S.chan_qd[ch], &S.chan_qdd[ch]);
     for (int k = 0; k < 3; ++k) constant_residue(S.offset[0][k], ctx->dt, &S.root_qd[k], &S.root_qdd[k]);
     ctx->scene_dirty = true;
+    ctx->scene_version += 1;
 }
 
 omo_status activate_scene(omo_ctx* ctx)
@@ -380,16 +413,89 @@ template <bool FK, bool IK, bool OUT, bool COUNT>
 omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B, const LaunchPlan& plan)
 {
     if (plan.smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
-    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<1, FK, IK, OUT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
+    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<FK, IK, OUT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing && !OUT) {
         OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
-    omo::objective_kernel<1, FK, IK, OUT, COUNT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
+    omo::objective_kernel<FK, IK, OUT, COUNT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
     OMO_CUDA(cudaGetLastError());
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1;
+    return OMO_OK;
+}
+
+// ---- scene-specialised kernels (omo_jit.hpp) ------------------------------------------------------------------------
+int jit_mode(omo_ctx* ctx)
+{
+    if (ctx->jit_mode < 0) {
+        const char* e = std::getenv("OMO_JIT");
+        ctx->jit_mode = e ? (std::atoi(e) == 0 ? 0 : (std::atoi(e) == 1 ? 1 : 2)) : 2;   // 2 = auto
+    }
+    return ctx->jit_mode;
+}
+
+// Compiles (once) and returns the specialised kernel of an instance, or nullptr when it cannot be had -- the caller
+// then launches the table-driven kernel, which is the same CUDA code driven by tables.
+omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
+{
+    omo_ctx::JitKernel& k = ctx->jit[(fk ? 1 : 0) | (ik ? 2 : 0) | (count ? 4 : 0)];
+    if (k.tried) return k.ok ? &k : nullptr;
+    k.tried = true;
+    omo_jit::Api& a = omo_jit::api();
+    if (!a.have_nvrtc() || !a.have_driver()) { ctx->jit_log = "JIT unavailable:" + a.error; return nullptr; }
+    const auto t0 = std::chrono::steady_clock::now();
+    omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk, ik, count);
+    if (const char* dump = std::getenv("OMO_JIT_DUMP")) {
+        if (FILE* fh = std::fopen((std::string(dump) + (fk ? "_fk" : "") + (ik ? "_ik" : "") + (count ? "_count" : "") + ".cu").c_str(), "w")) {
+            std::fputs(spec.source.c_str(), fh); std::fclose(fh);
+        }
+    }
+    std::vector<char> cubin;
+    std::string log;
+    if (!omo_jit::compile(spec.source, cubin, log)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+    if (a.cuModuleLoadData(&k.mod, cubin.data()) != 0) { ctx->jit_log = "cuModuleLoadData failed"; return nullptr; }
+    size_t bytes = 0;
+    if (a.cuModuleGetFunction(&k.fn, k.mod, "omo_jit_kernel") != 0 || a.cuModuleGetGlobal(&k.d_scene, &bytes, k.mod, "c_scene") != 0 ||
+        bytes != sizeof(OmoDevScene)) {
+        ctx->jit_log = "specialised module lacks omo_jit_kernel / c_scene";
+        a.cuModuleUnload(k.mod); k.mod = nullptr;
+        return nullptr;
+    }
+    k.smem = spec.smem_bytes;
+    if (a.cuFuncSetAttribute(k.fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)k.smem) != 0) {
+        ctx->jit_log = "cuFuncSetAttribute(max dynamic shared memory) failed";
+        a.cuModuleUnload(k.mod); k.mod = nullptr;
+        return nullptr;
+    }
+    a.cuFuncGetAttribute(&k.regs, 4 /* CU_FUNC_ATTRIBUTE_NUM_REGS */, k.fn);
+    k.compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    k.ok = true;
+    return &k;
+}
+
+omo_status launch_jit(omo_ctx* ctx, omo_ctx::JitKernel* k, const OmoEvalParams& P, int B, int n_tiles)
+{
+    omo_jit::Api& a = omo_jit::api();
+    if (k->uploaded_version != ctx->scene_version) {
+        OMO_CUDA(cudaMemcpyAsync(reinterpret_cast<void*>(k->d_scene), &ctx->hs, sizeof(OmoDevScene), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // hs is pageable host memory that may change after this call
+        k->uploaded_version = ctx->scene_version;
+    }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->timing) {
+        OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
+        OMO_CUDA(cudaEventRecord(e0, ctx->stream));
+    }
+    OmoEvalParams Pc = P;
+    void* args[] = {&Pc};
+    const int rc = a.cuLaunchKernel(k->fn, (unsigned)(B * n_tiles), 1, 1, kBlockThreads, 1, 1, (unsigned)k->smem,
+                                    reinterpret_cast<omo_jit::CUstream>(ctx->stream), args, nullptr);
+    if (rc != 0) return fail(ctx, OMO_CUDA_ERROR, "cuLaunchKernel(omo_jit_kernel) failed with CUresult " + std::to_string(rc));
+    if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
+    ctx->launches += 1;
+    ctx->jit_launches += 1;
     return OMO_OK;
 }
 
@@ -402,6 +508,18 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
     P.n_tiles = plan.n_tiles; P.T_out = plan.t_out;
     omo_status st;
+    // large launches run the scene-specialised kernel (auto: >= 64 K sample-evals; OMO_JIT=1 always, OMO_JIT=0 never)
+    const int mode = jit_mode(ctx);
+    if (!out && mode != 0 && (mode == 1 || (long long)B * ctx->N_s >= 65536)) {
+        if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
+            if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
+            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, d_f, d_terms);
+            OMO_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+            return OMO_OK;
+        }
+        if (mode == 1) return fail(ctx, OMO_CUDA_ERROR, "OMO_JIT=1 but the specialised kernel is unavailable: " + ctx->jit_log);
+    }
     if (out) st = ik ? launch_objective_t<true, true, true, false>(ctx, P, B, plan) : launch_objective_t<true, false, true, false>(ctx, P, B, plan);
     else if (ik) st = count ? launch_objective_t<true, true, false, true>(ctx, P, B, plan) : launch_objective_t<true, true, false, false>(ctx, P, B, plan);
     else if (fk) st = count ? launch_objective_t<true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false>(ctx, P, B, plan);
@@ -502,6 +620,7 @@ omo_status ensure_ready(omo_ctx* ctx)
             ctx->hs.static_tsq = acc;
         }
         ctx->scene_dirty = true;
+        ctx->scene_version += 1;
         const int n = ctx->N_s * 3 * ctx->J;
         omo::transpose_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_op, ctx->N_s, 3 * ctx->J, ctx->d_p_orig);
         OMO_CUDA(cudaGetLastError());
@@ -571,6 +690,7 @@ void omo_destroy(omo_ctx* ctx)
                     ctx->d_x0, ctx->d_p_orig, ctx->d_X, ctx->d_prep, ctx->d_dparam, ctx->d_partial, ctx->d_f, ctx->d_terms, ctx->d_flags,
                     ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters};
     for (void* p : ptrs) if (p) cudaFree(p);
+    for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -881,6 +1001,46 @@ omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* lau
         ctx->timed.clear();
         ctx->timing = reset > 0;  // reset = 1: (re)start timing; reset = -1: stop
     }
+    return OMO_OK;
+}
+
+omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const char* dump_prefix, char* log, int log_cap)
+{
+    if (!scene) return OMO_BAD_ARG;
+    omo_ctx* ctx = new omo_ctx();
+    omo_status st = build_tables(ctx, scene);
+    std::string msg;
+    if (st == OMO_OK) {
+        const bool ik = ctx->n_ik > 0;
+        omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk != 0 || ik, ik, count != 0);
+        std::vector<char> cubin;
+        std::string clog;
+        const bool ok = omo_jit::compile(spec.source, cubin, clog);
+        if (dump_prefix) {
+            if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cu").c_str(), "w")) { std::fputs(spec.source.c_str(), fh); std::fclose(fh); }
+            if (ok) if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cubin").c_str(), "wb")) { std::fwrite(cubin.data(), 1, cubin.size(), fh); std::fclose(fh); }
+        }
+        msg = "smem_slots=" + std::to_string(spec.n_smem_slots) + " thread_slots=" + std::to_string(spec.n_reg_slots) + " min_blocks=" +
+              std::to_string(spec.min_blocks) + " smem_bytes=" + std::to_string(spec.smem_bytes) + " cubin_bytes=" + std::to_string(cubin.size()) + "\n" + clog;
+        if (!ok) st = OMO_CUDA_ERROR;
+    } else {
+        msg = ctx->err;
+    }
+    if (log && log_cap > 0) { std::strncpy(log, msg.c_str(), (size_t)log_cap - 1); log[log_cap - 1] = 0; }
+    delete ctx;
+    return st;
+}
+
+omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int log_cap)
+{
+    if (!ctx) return OMO_BAD_ARG;
+    if (out4) {
+        out4[0] = ctx->jit_launches;
+        out4[1] = 0; out4[2] = 0; out4[3] = 0;
+        for (const auto& k : ctx->jit)
+            if (k.ok) { out4[1] += 1; out4[2] = std::max<unsigned long long>(out4[2], (unsigned long long)k.regs); out4[3] += (unsigned long long)k.compile_ms; }
+    }
+    if (log && log_cap > 0) { std::strncpy(log, ctx->jit_log.c_str(), (size_t)log_cap - 1); log[log_cap - 1] = 0; }
     return OMO_OK;
 }
 

@@ -10,8 +10,14 @@
 #ifndef OMO_MATH_CUH
 #define OMO_MATH_CUH
 
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <math.h>
+#else
+#ifndef INFINITY
+#define INFINITY __longlong_as_double(0x7ff0000000000000LL)
+#endif
+#endif
 
 namespace omo {
 

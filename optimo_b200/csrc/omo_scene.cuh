@@ -7,9 +7,17 @@
 #ifndef OMO_SCENE_CUH
 #define OMO_SCENE_CUH
 
+#ifdef __CUDACC_RTC__
+// NVRTC build (omo_jit.hpp): only the limits of include/omo.h are needed; omo.cu static_asserts that they agree.
+#define OMO_MAX_JOINTS 128
+#define OMO_MAX_IK 8
+#define OMO_MAX_IK_CHAIN 8
+#else
 #include "../../include/omo.h"
+#endif
 
 #define OMO_MAXJ OMO_MAX_JOINTS
+#define OMO_NT 128   // threads per block (compile-time: every stack / exchange access gets an immediate offset)
 #define OMO_SLOT 12  // doubles per stack slot: (f, sincos) or (v, a) or (L, t)
 
 // Per-body constants: the RBDL quantities InverseDynamics reads (Model::X_T[i].r, Model::I[i];

@@ -1,0 +1,433 @@
+// The per-thread tree walk of the objective kernels, as a set of force-inlined steps.
+//
+// One THREAD = one (candidate, time sample); one BLOCK = (candidate, tile of consecutive samples + 2-sample halo
+// each side). Two kernels drive these steps:
+//   * objective_kernel (omo_objective.cuh): a loop over the scene tables in constant memory -- works for any scene,
+//     compiled ahead of time by nvcc;
+//   * the scene-specialised kernel (omo_jit.cpp): the SAME steps emitted as straight-line code with every body index,
+//     stack slot, channel row and flag a literal, compiled for sm_100a at run time with NVRTC. Every table lookup,
+//     branch and address computation of the loop disappears and the body constants become constant-bank operands of
+//     the DFMAs.
+//
+// Restates, per (candidate, time sample):
+//   Core::SetStates           OptiMo/core_rbdl.cpp:108-166   (q from curves / IK, p from FK)
+//   CalculateFirst/SecondCentral  core_rbdl.cpp:28-95        (SECOND_ORDER_ACCURATE off)
+//   Joint::GetAffineRelativeTo{Parent,World}  OptiMo/joint.cpp:64-83   (T(offset) Rz Ry Rx)
+//   Core::CalculateCost       core_rbdl.cpp:307-346          (local_cost = |tau[3:]|^2 dt, weight w(t))
+//   D_traj                    core_rbdl.cpp:387-398
+// Template flags: FK = also run forward kinematics (positions; for D_traj and IK), IK = scene has IK chains,
+// OUT = write the per-sample OptimizationCache arrays (single-candidate launches; walks the FULL tree, every other
+// instance walks the pruned tree, see OmoDevScene::meta), COUNT = book executed curve / IK work.
+#ifndef OMO_WALK_CUH
+#define OMO_WALK_CUH
+
+#include "omo_kernels.cuh"
+
+namespace omo {
+
+// NREG > 0 (scene-specialised kernels only): stack slots numbered 256 + r live in the per-thread array rs[r][] instead of
+// shared memory; with literal slot numbers ptxas keeps them in registers or spills them to (L1-cached) local memory.
+// That is how deep trees keep several blocks per SM: only the most-used slots take shared memory.
+template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0>
+struct Walker {
+    static constexpr int NT = OMO_NT;
+    static constexpr int TREE = OUT ? 0 : 1;   // 0: every body, 1: candidate-independent subtrees pruned
+
+    const OmoEvalParams& P;
+    double* __restrict__ ex;    // [ex_rows][NT] stencil exchange: q of the dynamic channels
+    double* __restrict__ stk;   // [n_slots][OMO_SLOT][NT], already offset by tid
+    unsigned short* __restrict__ seg0;  // this warp's segment warm starts, [n_keyed]
+    const double* __restrict__ pc;      // this candidate's prepared control points
+    int tid, N, tile_end;
+    size_t dof;
+    bool sorted;
+    unsigned n_bez, n_newton, n_iksolve, n_ikiter;
+    int xbuf;
+
+    // state of the body visited last (v, a: also the parent state for the next one)
+    SV6 v, a, f;
+    double s0, c0, s1, c1, s2, c2;        // sin / cos of its Euler angles
+    double L[FK ? 9 : 1], W[FK ? 3 : 1];  // world affine handed to the next body's FK step
+    double tsq, dtr;                      // sum tau^2 (non-root DoFs), sum |p - p_original|^2
+    double t;                             // time of this sample
+    int s;                                // sample index (clamped into [0, N_s))
+    int idx;                              // position inside the block's window (exchange-buffer column)
+    bool owned, interior;
+    SV6 g;                                // force being folded back towards the root
+    SV6 groot;                            // OUT only: force folded into the root
+    double ikq[IK ? OMO_MAX_IK * 3 * OMO_MAX_IK_CHAIN : 1];
+    double rs[NREG > 0 ? NREG : 1][OMO_SLOT];
+
+    __device__ __forceinline__ Walker(const OmoEvalParams& P_) : P(P_) {}
+
+    // stack element c of slot sl
+    __device__ __forceinline__ double ld(const int sl, const int c) const
+    {
+        if (NREG > 0 && sl >= 256) return rs[sl - 256][c];
+        return stk[(size_t)(sl * OMO_SLOT + c) * NT];
+    }
+    __device__ __forceinline__ void st(const int sl, const int c, const double x)
+    {
+        if (NREG > 0 && sl >= 256) rs[sl - 256][c] = x;
+        else stk[(size_t)(sl * OMO_SLOT + c) * NT] = x;
+    }
+
+    // root state (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212): v = (0, qd), a = (0, qdd)
+    __device__ __forceinline__ void set_root()
+    {
+        const OmoDevScene& S = c_scene;
+        v.w0 = v.w1 = v.w2 = 0.0; a.w0 = a.w1 = a.w2 = 0.0;
+        v.l0 = interior ? S.root_qd[0] : 0.0; v.l1 = interior ? S.root_qd[1] : 0.0; v.l2 = interior ? S.root_qd[2] : 0.0;
+        a.l0 = interior ? S.root_qdd[0] : 0.0; a.l1 = interior ? S.root_qdd[1] : 0.0; a.l2 = interior ? S.root_qdd[2] : 0.0;
+    }
+
+    // ---- block / thread set-up -------------------------------------------------------------------------------------
+    // n_smem_slots: stack slots that live in shared memory (the scene's plan, or the specialised kernel's own)
+    __device__ __forceinline__ void begin(double* smem, const int n_smem_slots)
+    {
+        const OmoDevScene& S = c_scene;
+        tid = threadIdx.x;
+        const int cand = blockIdx.x / P.n_tiles;
+        const int tile = blockIdx.x - cand * P.n_tiles;
+        const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);
+        ex = smem;
+        double* stk0 = smem + ex_rows * NT;
+        stk = stk0 + tid;
+        N = P.N_s;
+        tile_end = min(N, (tile + 1) * P.T_out);
+        pc = P.prep + (size_t)cand * 6 * P.n_cp;
+        sorted = (__ldg(P.flags + cand) & 1u) != 0u;
+        dof = (size_t)3 * S.J;
+        n_bez = n_newton = n_iksolve = n_ikiter = 0u;
+        xbuf = 0;
+        // seg0[warp][n_keyed] (16-bit) sits behind the stack in dynamic shared memory
+        seg0 = reinterpret_cast<unsigned short*>(stk0 + (size_t)n_smem_slots * (OMO_SLOT * NT)) + (tid >> 5) * S.n_keyed;
+
+        // segment warm start: one binary search per keyed channel per WARP (for the time of its first lane; the lanes'
+        // times ascend), so each thread later only walks the few keys its own time lies beyond
+        if (sorted) {
+            const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2 + (tid & ~31), 0), N - 1));
+            for (int i = tid & 31; i < S.n_keyed; i += 32) {
+                const int ch = S.grp_list[i];
+                const double* __restrict__ T = pc + S.chan_pos[ch];
+                int lo = 0, hi = S.chan_n[ch];
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (__ldg(T + mid) <= t_first) lo = mid + 1; else hi = mid;
+                }
+                seg0[i] = (unsigned short)lo;
+            }
+        }
+        __syncwarp();
+
+        idx = tid;
+        const int s_raw = tile * P.T_out - 2 + idx;
+        s = min(max(s_raw, 0), N - 1);
+        owned = (idx >= 2) && (s_raw < tile_end) && (s_raw >= 0);
+        interior = (s >= 2) && (s <= N - 3);
+        t = __ldg(P.tgrid + s);
+        tsq = (!OUT && interior) ? S.static_tsq : 0.0;   // the pruned bodies' share (candidate-independent)
+        dtr = 0.0;
+        set_root();
+        f.w0 = f.w1 = f.w2 = f.l0 = f.l1 = f.l2 = 0.0;
+        g = f;
+        s0 = s1 = s2 = 0.0; c0 = c1 = c2 = 1.0;
+        if (OUT) groot = f;
+        if (OUT && owned) {
+            for (int k = 0; k < 3; ++k) {
+                P.o_q[s * dof + k] = S.offset[0][k];
+                P.o_qd[s * dof + k] = interior ? S.root_qd[k] : 0.0;
+                P.o_qdd[s * dof + k] = interior ? S.root_qdd[k] : 0.0;
+            }
+        }
+        if (FK) {
+            // root world affine = T(offset) Rz Ry Rx with the root's own rot channels (joint.cpp:64-74)
+            double e[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], t, sorted, n_bez, n_newton) : S.chan_const[k];
+            double sx, cx, sy, cy, sz, cz;
+            sincos_angle(e[0], &sx, &cx); sincos_angle(e[1], &sy, &cy); sincos_angle(e[2], &sz, &cz);
+            L[0] = cz * cy; L[1] = cz * sy * sx - sz * cx; L[2] = cz * sy * cx + sz * sx;
+            L[3] = sz * cy; L[4] = sz * sy * sx + cz * cx; L[5] = sz * sy * cx - cz * sx;
+            L[6] = -sy;     L[7] = cy * sx;                L[8] = cy * cx;
+            W[0] = S.offset[0][0]; W[1] = S.offset[0][1]; W[2] = S.offset[0][2];
+            if (P.p_orig) {
+                const double d0 = W[0] - __ldg(P.p_orig + (size_t)0 * N + s), d1 = W[1] - __ldg(P.p_orig + (size_t)1 * N + s),
+                             d2 = W[2] - __ldg(P.p_orig + (size_t)2 * N + s);
+                dtr += d0 * d0 + d1 * d1 + d2 * d2;
+            }
+            if (OUT && owned && P.o_p) { P.o_p[s * dof] = W[0]; P.o_p[s * dof + 1] = W[1]; P.o_p[s * dof + 2] = W[2]; }
+        }
+    }
+
+    // ---- stack traffic ---------------------------------------------------------------------------------------------
+    __device__ __forceinline__ void park_fs(const int sl, const bool ident)   // (f, sincos) of a body whose subtree opens
+    {
+        st(sl, 0, f.w0); st(sl, 1, f.w1); st(sl, 2, f.w2); st(sl, 3, f.l0); st(sl, 4, f.l1); st(sl, 5, f.l2);
+        if (!ident) { st(sl, 6, s0); st(sl, 7, c0); st(sl, 8, s1); st(sl, 9, c1); st(sl, 10, s2); st(sl, 11, c2); }
+    }
+    __device__ __forceinline__ void park_va(const int sl)   // (v, a) of a body with >= 2 children
+    {
+        st(sl, 0, v.w0); st(sl, 1, v.w1); st(sl, 2, v.w2); st(sl, 3, v.l0); st(sl, 4, v.l1); st(sl, 5, v.l2);
+        st(sl, 6, a.w0); st(sl, 7, a.w1); st(sl, 8, a.w2); st(sl, 9, a.l0); st(sl, 10, a.l1); st(sl, 11, a.l2);
+    }
+    __device__ __forceinline__ void load_va(const int sl)
+    {
+        v.w0 = ld(sl, 0); v.w1 = ld(sl, 1); v.w2 = ld(sl, 2); v.l0 = ld(sl, 3); v.l1 = ld(sl, 4); v.l2 = ld(sl, 5);
+        a.w0 = ld(sl, 6); a.w1 = ld(sl, 7); a.w2 = ld(sl, 8); a.l0 = ld(sl, 9); a.l1 = ld(sl, 10); a.l2 = ld(sl, 11);
+    }
+    __device__ __forceinline__ void park_fk(const int sl)   // world affine (L, W) of a body with >= 2 children
+    {
+        if (FK) {
+#pragma unroll
+            for (int c = 0; c < 9; ++c) st(sl, c, L[c]);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) st(sl, 9 + c, W[c]);
+        }
+    }
+    __device__ __forceinline__ void load_fk(const int sl)
+    {
+        if (FK) {
+#pragma unroll
+            for (int c = 0; c < 9; ++c) L[c] = ld(sl, c);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) W[c] = ld(sl, 9 + c);
+        }
+    }
+
+    // ---- backward pass ---------------------------------------------------------------------------------------------
+    // tau = S^T fk of body k (books |tau|^2), g = X_lambda^T fk (Dynamics.cc:87-104)
+    __device__ __forceinline__ void finalize(const int k, const bool ident, const SV6& fk, const double a0, const double b0, const double a1,
+                                             const double b1, const double a2, const double b2)
+    {
+        const OmoDevScene& S = c_scene;
+        double t0, t1, t2;
+        const double r0 = S.body[k].r[0], r1 = S.body[k].r[1], r2 = S.body[k].r[2];
+        SV6 gn;
+        if (ident) rnea_backward_identity(r0, r1, r2, fk, gn, t0, t1, t2);
+        else rnea_backward(r0, r1, r2, a0, b0, a1, b1, a2, b2, fk, gn, t0, t1, t2);
+        g = gn;
+        tsq = fma(t0, t0, fma(t1, t1, fma(t2, t2, tsq)));
+        if (OUT && owned) { P.o_tau[s * dof + 3 * k] = t0; P.o_tau[s * dof + 3 * k + 1] = t1; P.o_tau[s * dof + 3 * k + 2] = t2; }
+    }
+    // the body just visited is a leaf of the walk: fold it
+    __device__ __forceinline__ void fold_leaf(const int b, const bool ident) { finalize(b, ident, f, s0, c0, s1, c1, s2, c2); }
+    // ancestor k (parked in slot sl) is finished: add the force coming up and fold it
+    __device__ __forceinline__ void fold_up(const int k, const int sl, const bool ident)
+    {
+        SV6 fk;
+        fk.w0 = ld(sl, 0) + g.w0; fk.w1 = ld(sl, 1) + g.w1; fk.w2 = ld(sl, 2) + g.w2;
+        fk.l0 = ld(sl, 3) + g.l0; fk.l1 = ld(sl, 4) + g.l1; fk.l2 = ld(sl, 5) + g.l2;
+        if (ident) finalize(k, true, fk, 0.0, 1.0, 0.0, 1.0, 0.0, 1.0);
+        else finalize(k, false, fk, ld(sl, 6), ld(sl, 7), ld(sl, 8), ld(sl, 9), ld(sl, 10), ld(sl, 11));
+    }
+    // the walk continues below ancestor `stop` (slot sl): leave the force with it
+    __device__ __forceinline__ void fold_into(const int sl)
+    {
+        st(sl, 0, ld(sl, 0) + g.w0); st(sl, 1, ld(sl, 1) + g.w1); st(sl, 2, ld(sl, 2) + g.w2);
+        st(sl, 3, ld(sl, 3) + g.l0); st(sl, 4, ld(sl, 4) + g.l1); st(sl, 5, ld(sl, 5) + g.l2);
+    }
+    __device__ __forceinline__ void fold_root()
+    {
+        if (OUT) { groot.w0 += g.w0; groot.w1 += g.w1; groot.w2 += g.w2; groot.l0 += g.l0; groot.l1 += g.l1; groot.l2 += g.l2; }
+    }
+
+    // ---- sampling --------------------------------------------------------------------------------------------------
+    // IK chain h is rooted at the body about to be visited: solve it for this sample (joint.cpp:38-44, ikhandler.cpp:103-164)
+    __device__ __forceinline__ void ik_chain(const int h)
+    {
+        if (!IK) return;
+        const OmoDevScene& S = c_scene;
+        double tw[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            tw[k] = (S.ik_chan_n[h][k] > 0) ? eval_channel(pc, P.n_cp, S.ik_chan_pos[h][k], S.ik_chan_n[h][k], t, sorted, n_bez, n_newton)
+                                            : S.ik_chan_const[h][k];
+        double Lp[9], tp[3];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) Lp[c] = FK ? L[c] : 0.0;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) tp[c] = FK ? W[c] : 0.0;
+        unsigned it = 0;
+        ik_solve(h, Lp, tp, tw, ikq + h * 3 * OMO_MAX_IK_CHAIN, it);
+        if (owned) { n_ikiter += it; n_iksolve += 1u; }
+    }
+
+    // up to three keyed joint channels (entries i0.. of grp_list; ch < 0 = unused) sampled in lockstep into the exchange rows
+    __device__ __forceinline__ void curve_triple(const int i0, const int ch0, const int ch1, const int ch2)
+    {
+        const OmoDevScene& S = c_scene;
+        const int ch[3] = {ch0, ch1, ch2};
+        int pos[3], nn[3], row[3], sg[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const bool on = ch[k] >= 0;
+            const int c = on ? ch[k] : 0;
+            pos[k] = on ? S.chan_pos[c] : 0; nn[k] = on ? S.chan_n[c] : 0; row[k] = on ? S.chan_row[c] : 0;
+            sg[k] = on ? seg0[i0 + k] : 0;
+        }
+        double val[3];
+        unsigned eb = 0, en = 0;
+        eval_channels<3, COUNT>(pc, P.n_cp, pos, nn, sg, t, sorted, val, eb, en);
+        if (COUNT && owned) { n_bez += eb; n_newton += en; }   // halo samples repeat a neighbour tile's work
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (nn[k] > 0) ex[row[k] * NT + idx] = val[k];
+    }
+    __device__ __forceinline__ void group_sync() { __syncthreads(); }
+
+    // ---- forward step of a joint frozen at zero angles: E = I, qd = qdd = 0 exactly --------------------------------
+    __device__ __forceinline__ void body_ident(const int b)
+    {
+        const OmoDevScene& S = c_scene;
+        if (OUT && owned) {
+            const size_t o = s * dof + 3 * b;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { P.o_q[o + k] = 0.0; P.o_qd[o + k] = 0.0; P.o_qdd[o + k] = 0.0; }
+        }
+        SV6 vn, an;
+        rnea_forward_identity(S.body[b], v, a, vn, an, f);
+        v = vn; a = an;
+    }
+
+    // ---- forward step of a general EulerXYZ joint: angles (exchange rows / constants / IK), stencils
+    // (core_rbdl.cpp:28-95), sin / cos, jcalc + RNEA forward (Joint.cc:100-139, Dynamics.cc:39-73) ------------------
+    // mask bit k: channel k comes from exchange row rowK; ikh >= 0: all three come from IK handler ikh, chain position ik_idx.
+    __device__ __forceinline__ void body_general(const int b, const int mask_in, const int row0, const int row1, const int row2,
+                                                 const int ikh, const int ik_idx)
+    {
+        const OmoDevScene& S = c_scene;
+        const int mask = (IK && ikh >= 0) ? 7 : mask_in;
+        double q[3], qd[3], qdd[3], ss[3], cc[3];
+        int rowk[3] = {row0, row1, row2};
+        if (IK && ikh >= 0) {
+            // IK-driven joint: its angles were solved per thread; exchange them through 3 dedicated double-buffered rows
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                rowk[k] = S.n_ex_rows + xbuf * 3 + k;
+                ex[rowk[k] * NT + idx] = ikq[ikh * 3 * OMO_MAX_IK_CHAIN + 3 * ik_idx + k];
+            }
+            __syncthreads();
+            xbuf ^= 1;
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (mask >> k & 1) {
+                const double* __restrict__ row = ex + rowk[k] * NT;
+                // stencil neighbours inside the block (clamped for the halo samples, whose results are unused)
+                const double m2 = row[max(idx - 2, 0)], m1 = row[max(idx - 1, 0)], x = row[idx];
+                const double p1 = row[min(idx + 1, NT - 1)], p2 = row[min(idx + 2, NT - 1)];
+                q[k] = x;
+                if (interior) {
+                    qd[k] = (-p2 + 8.0 * p1 - 8.0 * m1 + m2) * P.inv_12dt;
+                    qdd[k] = (-p2 + 16.0 * p1 - 30.0 * x + 16.0 * m1 - m2) * P.inv_12dt2;
+                } else if (s == 0) {
+                    qd[k] = (p1 - x) * P.inv_dt;
+                    qdd[k] = (p2 - 2.0 * p1 + x) * P.inv_2dt2;
+                } else if (s == N - 1) {
+                    qd[k] = (x - m1) * P.inv_dt;
+                    qdd[k] = (x - 2.0 * m1 + m2) * P.inv_2dt2;
+                } else {
+                    qd[k] = (p1 - m1) * P.inv_2dt;
+                    qdd[k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
+                }
+                sincos_angle(x, &ss[k], &cc[k]);
+            } else {
+                q[k] = S.chan_const[3 * b + k]; ss[k] = S.chan_sin[3 * b + k]; cc[k] = S.chan_cos[3 * b + k];
+                qd[k] = interior ? S.chan_qd[3 * b + k] : 0.0;
+                qdd[k] = interior ? S.chan_qdd[3 * b + k] : 0.0;
+            }
+        }
+        s0 = ss[0]; s1 = ss[1]; s2 = ss[2]; c0 = cc[0]; c1 = cc[1]; c2 = cc[2];
+        if (OUT && owned) {
+            const size_t o = s * dof + 3 * b;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { P.o_q[o + k] = q[k]; P.o_qd[o + k] = qd[k]; P.o_qdd[o + k] = qdd[k]; }
+        }
+        SV6 vn, an;
+        rnea_forward(S.body[b], s0, c0, s1, c1, s2, c2, qd[0], qd[1], qd[2], qdd[0], qdd[1], qdd[2], v, a, vn, an, f);
+        v = vn; a = an;
+    }
+
+    // ---- forward kinematics: p_b and the world affine handed to b's children (joint.cpp:64-83) --------------------------
+    __device__ __forceinline__ void fk_step(const int b, const bool has_child, const bool ident)
+    {
+        if (!FK) return;
+        const OmoDevScene& S = c_scene;
+        const double o0 = S.offset[b][0], o1 = S.offset[b][1], o2 = S.offset[b][2];
+        const double p0 = fma(L[0], o0, fma(L[1], o1, fma(L[2], o2, W[0])));
+        const double p1 = fma(L[3], o0, fma(L[4], o1, fma(L[5], o2, W[1])));
+        const double p2 = fma(L[6], o0, fma(L[7], o1, fma(L[8], o2, W[2])));
+        if (P.p_orig) {
+            const double d0 = p0 - __ldg(P.p_orig + (size_t)(3 * b) * N + s), d1 = p1 - __ldg(P.p_orig + (size_t)(3 * b + 1) * N + s),
+                         d2 = p2 - __ldg(P.p_orig + (size_t)(3 * b + 2) * N + s);
+            dtr += d0 * d0 + d1 * d1 + d2 * d2;
+        }
+        if (OUT && owned && P.o_p) { P.o_p[s * dof + 3 * b] = p0; P.o_p[s * dof + 3 * b + 1] = p1; P.o_p[s * dof + 3 * b + 2] = p2; }
+        if (has_child) {
+            if (!ident) {
+                // L <- L * Rz(q2) Ry(q1) Rx(q0)
+                const double R00 = c2 * c1, R01 = c2 * s1 * s0 - s2 * c0, R02 = c2 * s1 * c0 + s2 * s0;
+                const double R10 = s2 * c1, R11 = s2 * s1 * s0 + c2 * c0, R12 = s2 * s1 * c0 - c2 * s0;
+                const double R20 = -s1, R21 = c1 * s0, R22 = c1 * c0;
+                double n[9];
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    n[3 * r] = fma(L[3 * r], R00, fma(L[3 * r + 1], R10, L[3 * r + 2] * R20));
+                    n[3 * r + 1] = fma(L[3 * r], R01, fma(L[3 * r + 1], R11, L[3 * r + 2] * R21));
+                    n[3 * r + 2] = fma(L[3 * r], R02, fma(L[3 * r + 1], R12, L[3 * r + 2] * R22));
+                }
+#pragma unroll
+                for (int c = 0; c < 9; ++c) L[c] = n[c];
+            }
+            W[0] = p0; W[1] = p1; W[2] = p2;
+        }
+    }
+
+    // ---- cost of the sample and block reduction (local_cost = |tau[3:]|^2 dt, core_rbdl.cpp:331-334) ----------------
+    __device__ __forceinline__ void finish(double* smem)
+    {
+        double wc = 0.0, wt = 0.0;
+        const double local = tsq * P.dt;
+        if (OUT && owned) {
+            // tau[0:3] of the TranslationXYZ root = linear part of the force folded into body 1 (Dynamics.cc:91-92)
+            P.o_tau[s * dof] = groot.l0; P.o_tau[s * dof + 1] = groot.l1; P.o_tau[s * dof + 2] = groot.l2;
+            P.o_local[s] = local;
+        }
+        if (owned) {
+            wc = __ldg(P.wcost + s) * local;
+            if (FK) wt = P.w_traj * dtr * P.dt;
+        }
+        __syncthreads();  // everyone is done with the exchange buffers
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            wc += __shfl_down_sync(0xffffffffu, wc, o);
+            wt += __shfl_down_sync(0xffffffffu, wt, o);
+        }
+        double* red = smem;
+        if ((tid & 31) == 0) { red[2 * (tid >> 5)] = wc; red[2 * (tid >> 5) + 1] = wt; }
+        __syncthreads();
+        if (tid == 0) {
+            double C = 0.0, D = 0.0;
+            for (int w = 0; w < (NT >> 5); ++w) { C += red[2 * w]; D += red[2 * w + 1]; }
+            P.partial[(size_t)blockIdx.x * 2] = C;
+            P.partial[(size_t)blockIdx.x * 2 + 1] = D;
+        }
+        if (COUNT && P.counters) {
+            unsigned cb = n_bez, cn = n_newton, ci = n_iksolve, cj = n_ikiter;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                cb += __shfl_down_sync(0xffffffffu, cb, o); cn += __shfl_down_sync(0xffffffffu, cn, o);
+                ci += __shfl_down_sync(0xffffffffu, ci, o); cj += __shfl_down_sync(0xffffffffu, cj, o);
+            }
+            if ((tid & 31) == 0) {
+                atomicAdd(P.counters + 0, (unsigned long long)cb); atomicAdd(P.counters + 1, (unsigned long long)cn);
+                atomicAdd(P.counters + 2, (unsigned long long)ci); atomicAdd(P.counters + 3, (unsigned long long)cj);
+            }
+        }
+    }
+};
+
+}  // namespace omo
+#endif

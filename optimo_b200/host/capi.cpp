@@ -182,6 +182,17 @@ int optimo_perform_optimization(void* h, int explicit_termination, double* final
     });
 }
 
+int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump_prefix, char* log, int cap)
+{
+    int status = 0;
+    const int rc = guarded([&] {
+        std::string l;
+        status = C(h)->ProbeSpecialisedKernel(fk != 0, count != 0, dump_prefix ? dump_prefix : "", &l);
+        if (log && cap > 0) { std::strncpy(log, l.c_str(), static_cast<size_t>(cap) - 1); log[cap - 1] = 0; }
+    });
+    return rc != 0 ? rc : (status == 0 ? 0 : 1);
+}
+
 void optimo_record_solve_trace(void* h, int enable) { C(h)->record_solve_trace_ = enable != 0; }
 int optimo_solve_trace_size(void* h, int* rows, int* dim)
 {

@@ -306,9 +306,30 @@ omo_ctx* Core::Engine()
     d.n_ik = static_cast<int>(iks.size()); d.ik_root = ik_root.data(); d.ik_end = ik_end.data();
     d.n_channels = static_cast<int>(chan_const.size()); d.chan_const = chan_const.data(); d.chan_first_cp = first_cp.data();
     d.chan_n_cp = n_cp_ch.data(); d.n_cp = cp_total; d.chain = chain.data();
+    if (probe_only_) {
+        // host-only check of the scene-specialised kernel (include/omo.h: omo_jit_probe); no device is touched
+        std::vector<char> log(1 << 16, 0);
+        const omo_status ps = omo_jit_probe(&d, probe_fk_, probe_count_, probe_prefix_.empty() ? nullptr : probe_prefix_.c_str(), log.data(),
+                                            static_cast<int>(log.size()));
+        probe_log_ = log.data();
+        probe_status_ = static_cast<int>(ps);
+        return nullptr;
+    }
     const omo_status st = omo_create(&d, device_, &engine_);
     if (st != OMO_OK) { engine_ = nullptr; throw engine_error(std::string("omo_create: ") + omo_last_error(nullptr)); }
     return engine_;
+}
+
+int Core::ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_prefix, std::string* log)
+{
+    omo_ctx* keep = engine_;
+    engine_ = nullptr;
+    probe_only_ = true; probe_fk_ = fk ? 1 : 0; probe_count_ = count ? 1 : 0; probe_prefix_ = dump_prefix;
+    try { Engine(); } catch (...) { probe_only_ = false; engine_ = keep; throw; }
+    probe_only_ = false;
+    engine_ = keep;
+    if (log) *log = probe_log_;
+    return probe_status_;
 }
 
 /// Snapshots the state the objective reads (weights, kernels, cyclic flag, window, x_original) into the engine.

@@ -101,6 +101,9 @@ public:
     int GetDevice() const { return device_; }
     /// The engine behind the objective; created lazily (never before main), rebuilt when the scene changes.
     omo_ctx* Engine();
+    /// Generates and NVRTC-compiles the scene-specialised objective kernel of the current scene on the host (no GPU
+    /// needed); returns the omo_status, `log` gets the placement summary + compiler log. See omo_jit_probe.
+    int ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_prefix, std::string* log);
     /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
     void InitializeDynamicsModel();
 
@@ -121,6 +124,9 @@ private:
     std::vector<GaussianKernel> kernels_;
     VecN x_original_;
     omo_ctx* engine_ = nullptr;
+    bool probe_only_ = false;
+    int probe_fk_ = 0, probe_count_ = 0, probe_status_ = 0;
+    std::string probe_prefix_, probe_log_;
     int device_ = 0;
 
     std::mutex optimization_cache_mutex_;
