@@ -287,7 +287,7 @@ def run_ours(args):
     from oracle import oracle as O
     cores = os.cpu_count() or 1
     sample = max(cores, min(B, 64 * cores))
-    if args.workload == "grad" or world > 1:
+    if args.workload == "grad" or world > 1 or args.no_cpu_baseline:
         cpu = None
     else:
         leg = cpu_reference_leg(scene, sample, 0, x0)
@@ -327,6 +327,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="stick240", choices=["stick240", "tree64", "grad"])
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="development runs: skip the timed CPU leg (cpu_baseline = null)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -178,6 +178,11 @@ omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* lau
 omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int log_cap);
 omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const char* dump_prefix, char* log, int log_cap);
 
+/* Device self-test of the hand-scheduled FP64 division used by the curve solver (omo_kernels.cuh: div_rn_fast;
+ * it replaces the `f / f'` of SolveCubic, OptiMo/curve.cpp:50): q_fast[i] = the branch-free sequence, ok[i] = its
+ * validity test, q_ref[i] = the compiler's IEEE division. Wherever ok[i] != 0, q_fast[i] must equal q_ref[i] bit for bit. */
+omo_status omo_selftest_division(omo_ctx* ctx, const double* num, const double* den, int n, double* q_fast, double* q_ref, int* ok);
+
 /* Sustained dependent-free DFMA throughput of the device in FLOP/s (roofline denominator; runs ~ms). */
 omo_status omo_measure_dfma_peak(omo_ctx* ctx, double* flops_per_s);
 

@@ -136,6 +136,7 @@ _OMO_SIG = {
     "omo_kernel_timing": (ci, [_vp, ci, _dp, _ip]),
     "omo_measure_dfma_peak": (ci, [_vp, _dp]),
     "omo_jit_info": (ci, [_vp, C.POINTER(_ull), cs, ci]),
+    "omo_selftest_division": (ci, [_vp, _dp, _dp, ci, _dp, _dp, _ip]),
 }
 for _n, (_r, _a) in _OMO_SIG.items():
     _sig(_omo, _n, _r, _a)
@@ -296,6 +297,16 @@ class Engine:
         self._ck(_omo.omo_jit_info(self.h, out, buf, len(buf)), "omo_jit_info")
         return {"launches": int(out[0]), "instances": int(out[1]), "max_registers": int(out[2]), "compile_ms": int(out[3]),
                 "log": buf.value.decode(errors="replace")}
+
+    def selftest_division(self, num, den):
+        """(q_fast, q_ref, ok) of the curve solver's hand-scheduled division on the device (include/omo.h)."""
+        num = np.ascontiguousarray(num, dtype=np.float64)
+        den = np.ascontiguousarray(den, dtype=np.float64)
+        n = num.size
+        qf, qr, ok = np.empty(n), np.empty(n), np.empty(n, dtype=np.int32)
+        self._ck(_omo.omo_selftest_division(self.h, num.ctypes.data_as(_dp), den.ctypes.data_as(_dp), n, qf.ctypes.data_as(_dp),
+                                            qr.ctypes.data_as(_dp), ok.ctypes.data_as(_ip)), "omo_selftest_division")
+        return qf, qr, ok
 
     def dfma_peak(self):
         v = C.c_double(0.0)

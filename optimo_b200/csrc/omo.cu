@@ -52,7 +52,8 @@ struct omo_ctx {
         omo_jit::CUmodule mod = nullptr;
         omo_jit::CUfunction fn = nullptr;
         omo_jit::CUdeviceptr d_scene = 0;
-        size_t smem = 0;
+        size_t smem = 0, item_smem = 0;
+        int sub = 1;
         int regs = 0;
         unsigned long long uploaded_version = 0;
         double compile_ms = 0.0;
@@ -89,6 +90,8 @@ struct omo_ctx {
     int cap = 0;
     double *d_X = nullptr, *d_prep = nullptr, *d_dparam = nullptr, *d_partial = nullptr, *d_f = nullptr, *d_terms = nullptr;
     unsigned* d_flags = nullptr;
+    double* d_seg = nullptr;              // [cap][n_cp][OMO_SEGD] prepared segments
+    unsigned short* d_tile_seg = nullptr; // [cap][n_tiles][n_keyed]
     // single-candidate outputs (OptimizationCache)
     double *d_oq = nullptr, *d_oqd = nullptr, *d_oqdd = nullptr, *d_otau = nullptr, *d_olocal = nullptr, *d_op = nullptr;
     int out_cap_samples = 0;
@@ -379,6 +382,9 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
     if ((st = dev_alloc(ctx, &ctx->d_prep, (size_t)cap * 6 * ctx->n_cp)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_dparam, (size_t)cap)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_flags, (size_t)cap)) != OMO_OK) return st;
+    // + OMO_SEGW records of slack: the staging copy of the last channel never reads past the allocation
+    if ((st = dev_alloc(ctx, &ctx->d_seg, ((size_t)cap * ctx->n_cp + OMO_SEGW) * OMO_SEGD)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_tile_seg, (size_t)cap * std::max(ctx->n_tiles, 1) * std::max(ctx->hs.n_keyed, 1))) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_partial, (size_t)cap * std::max(ctx->n_tiles, 1) * 2)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_f, (size_t)cap)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_terms, (size_t)cap * 3)) != OMO_OK) return st;
@@ -454,7 +460,7 @@ omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
     }
     std::vector<char> cubin;
     std::string log;
-    if (!omo_jit::compile(spec.source, cubin, log)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+    if (!omo_jit::compile(spec.source, cubin, log, spec.sub)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
     if (a.cuModuleLoadData(&k.mod, cubin.data()) != 0) { ctx->jit_log = "cuModuleLoadData failed"; return nullptr; }
     size_t bytes = 0;
     if (a.cuModuleGetFunction(&k.fn, k.mod, "omo_jit_kernel") != 0 || a.cuModuleGetGlobal(&k.d_scene, &bytes, k.mod, "c_scene") != 0 ||
@@ -463,7 +469,7 @@ omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
         a.cuModuleUnload(k.mod); k.mod = nullptr;
         return nullptr;
     }
-    k.smem = spec.smem_bytes;
+    k.smem = spec.smem_bytes; k.item_smem = spec.item_smem; k.sub = spec.sub;
     if (a.cuFuncSetAttribute(k.fn, 8 /* CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES */, (int)k.smem) != 0) {
         ctx->jit_log = "cuFuncSetAttribute(max dynamic shared memory) failed";
         a.cuModuleUnload(k.mod); k.mod = nullptr;
@@ -489,8 +495,10 @@ omo_status launch_jit(omo_ctx* ctx, omo_ctx::JitKernel* k, const OmoEvalParams& 
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
     OmoEvalParams Pc = P;
+    Pc.n_items = B * n_tiles;
+    Pc.smem_stride = (int)(k->item_smem / sizeof(double));
     void* args[] = {&Pc};
-    const int rc = a.cuLaunchKernel(k->fn, (unsigned)(B * n_tiles), 1, 1, kBlockThreads, 1, 1, (unsigned)k->smem,
+    const int rc = a.cuLaunchKernel(k->fn, (unsigned)((B * n_tiles + k->sub - 1) / k->sub), 1, 1, kBlockThreads * k->sub, 1, 1, (unsigned)k->smem,
                                     reinterpret_cast<omo_jit::CUstream>(ctx->stream), args, nullptr);
     if (rc != 0) return fail(ctx, OMO_CUDA_ERROR, "cuLaunchKernel(omo_jit_kernel) failed with CUresult " + std::to_string(rc));
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
@@ -506,7 +514,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     if (ik || out) fk = true;
     const bool count = P.counters != nullptr && !out;
     const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
-    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out;
+    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.n_items = B * plan.n_tiles; P.smem_stride = 0;
     omo_status st;
     // large launches run the scene-specialised kernel (auto: >= 64 K sample-evals; OMO_JIT=1 always, OMO_JIT=0 never)
     const int mode = jit_mode(ctx);
@@ -534,7 +542,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
 void fill_params(const omo_ctx* ctx, OmoEvalParams& P)
 {
     std::memset(&P, 0, sizeof(P));
-    P.prep = ctx->d_prep; P.flags = ctx->d_flags; P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = ctx->d_partial;
+    P.prep = ctx->d_prep; P.flags = ctx->d_flags; P.seg = ctx->d_seg; P.tile_seg = ctx->d_tile_seg; P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = ctx->d_partial;
     P.N_s = ctx->N_s; P.n_cp = ctx->n_cp;
     const double dt = ctx->dt;
     P.dt = dt; P.inv_dt = 1.0 / dt; P.inv_2dt = 1.0 / (2.0 * dt); P.inv_12dt = 1.0 / (12.0 * dt);
@@ -550,6 +558,8 @@ omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
     Q.cp_of_pos = ctx->d_cp_of_pos; Q.first_of_pos = ctx->d_first_of_pos; Q.last_of_pos = ctx->d_last_of_pos; Q.next_same = ctx->d_next_same;
     Q.prep = ctx->d_prep; Q.flags = ctx->d_flags; Q.dparam = ctx->d_dparam;
     Q.n_cp = ctx->n_cp; Q.D = ctx->D; Q.cyclic = ctx->cyclic;
+    Q.seg = ctx->d_seg; Q.tile_seg = ctx->d_tile_seg; Q.tgrid = ctx->d_tgrid;
+    Q.N_s = ctx->N_s; Q.T_out = ctx->T_out; Q.n_tiles = ctx->n_tiles; Q.n_keyed = ctx->hs.n_keyed;
     omo::prepare_kernel<<<B, 128, 0, ctx->stream>>>(Q);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
@@ -688,7 +698,7 @@ void omo_destroy(omo_ctx* ctx)
     }
     void* ptrs[] = {ctx->d_cp_of_pos, ctx->d_first_of_pos, ctx->d_last_of_pos, ctx->d_next_same, ctx->d_tgrid, ctx->d_wparam, ctx->d_wcost,
                     ctx->d_x0, ctx->d_p_orig, ctx->d_X, ctx->d_prep, ctx->d_dparam, ctx->d_partial, ctx->d_f, ctx->d_terms, ctx->d_flags,
-                    ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters};
+                    ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters, ctx->d_seg, ctx->d_tile_seg};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -1015,7 +1025,7 @@ omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const c
         omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk != 0 || ik, ik, count != 0);
         std::vector<char> cubin;
         std::string clog;
-        const bool ok = omo_jit::compile(spec.source, cubin, clog);
+        const bool ok = omo_jit::compile(spec.source, cubin, clog, spec.sub);
         if (dump_prefix) {
             if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cu").c_str(), "w")) { std::fputs(spec.source.c_str(), fh); std::fclose(fh); }
             if (ok) if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cubin").c_str(), "wb")) { std::fwrite(cubin.data(), 1, cubin.size(), fh); std::fclose(fh); }
@@ -1068,6 +1078,29 @@ omo_status omo_measure_dfma_peak(omo_ctx* ctx, double* flops_per_s)
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d_out);
     *flops_per_s = best;
+    return OMO_OK;
+}
+
+omo_status omo_selftest_division(omo_ctx* ctx, const double* num, const double* den, int n, double* q_fast, double* q_ref, int* ok)
+{
+    if (!ctx || !num || !den || !q_fast || !q_ref || !ok || n <= 0) return OMO_BAD_ARG;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    double *d_n = nullptr, *d_d = nullptr, *d_q = nullptr, *d_r = nullptr;
+    int* d_ok = nullptr;
+    const size_t bytes = (size_t)n * sizeof(double);
+    OMO_CUDA(cudaMalloc((void**)&d_n, bytes)); OMO_CUDA(cudaMalloc((void**)&d_d, bytes));
+    OMO_CUDA(cudaMalloc((void**)&d_q, bytes)); OMO_CUDA(cudaMalloc((void**)&d_r, bytes));
+    OMO_CUDA(cudaMalloc((void**)&d_ok, (size_t)n * sizeof(int)));
+    OMO_CUDA(cudaMemcpyAsync(d_n, num, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    OMO_CUDA(cudaMemcpyAsync(d_d, den, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    omo::division_selftest_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(d_n, d_d, n, d_q, d_r, d_ok);
+    OMO_CUDA(cudaGetLastError());
+    OMO_CUDA(cudaMemcpyAsync(q_fast, d_q, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaMemcpyAsync(q_ref, d_r, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaMemcpyAsync(ok, d_ok, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_n); cudaFree(d_d); cudaFree(d_q); cudaFree(d_r); cudaFree(d_ok);
+    ctx->launches += 1;
     return OMO_OK;
 }
 

@@ -18,7 +18,20 @@
 
 #define OMO_MAXJ OMO_MAX_JOINTS
 #define OMO_NT 128   // threads per block (compile-time: every stack / exchange access gets an immediate offset)
+// OMO_SUB (scene-specialised kernels): (candidate, tile) work items fused into one thread block, each on its own
+// OMO_NT threads and its own slice of dynamic shared memory; they only share the block barriers -- and therefore
+// march through the straight-line code together, so that one instruction-cache line serves all of them.
+#ifndef OMO_SUB
+#define OMO_SUB 1
+#endif
 #define OMO_SLOT 12  // doubles per stack slot: (f, sincos) or (v, a) or (L, t)
+// Prepared Bezier segments (prepare_kernel -> objective kernels): one record of OMO_SEGD doubles per chain position
+// `pos` that closes a segment (pos-1 -> pos of the same channel):
+//   0: p0 = t_start   1: te = t_end   2: a   3: b   4: c   5: 3a   (time cubic, curve.cpp:85-88)   6..9: v0 v1 v2 v3
+// The scene-specialised kernel stages, per keyed channel, the OMO_SEGW records starting at the segment that holds the
+// block's first sample into shared memory (cp.async) and solves from there.
+#define OMO_SEGD 10
+#define OMO_SEGW 4
 
 // Per-body constants: the RBDL quantities InverseDynamics reads (Model::X_T[i].r, Model::I[i];
 // external/rbdl-v2.5.0/src/Model.cc:258-464, include/rbdl/SpatialAlgebraOperators.h:116-128).
@@ -87,7 +100,11 @@ struct OmoEvalParams {
     const double* wcost;    // [N_s] time-varying cost weight (core.cpp:191-199)
     const double* p_orig;   // [3J][N_s] joint positions of the original motion
     double* partial;        // [B][n_tiles][2]: (sum w*local_cost, sum w_traj*|p-p0|^2*dt)
+    const double* seg;      // [B][n_cp][OMO_SEGD] prepared segments, chain order
+    const unsigned short* tile_seg;  // [B][n_tiles][n_keyed] number of keys with time <= the tile's first sample time
     int N_s, n_tiles, T_out, n_cp;
+    int n_items;      // B * n_tiles work items (one per OMO_NT threads)
+    int smem_stride;  // doubles of dynamic shared memory per work item (used when OMO_SUB > 1)
     double dt, inv_dt, inv_2dt, inv_12dt, inv_dt2, inv_2dt2, inv_12dt2;
     double w_traj;
     // optional per-sample outputs of candidate 0 (OptimizationCache, core.h:120-152); sample-major

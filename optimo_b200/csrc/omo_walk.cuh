@@ -22,13 +22,16 @@
 #define OMO_WALK_CUH
 
 #include "omo_kernels.cuh"
+#include "omo_rnea_z.cuh"
 
 namespace omo {
 
 // NREG > 0 (scene-specialised kernels only): stack slots numbered 256 + r live in the per-thread array rs[r][] instead of
 // shared memory; with literal slot numbers ptxas keeps them in registers or spills them to (L1-cached) local memory.
 // That is how deep trees keep several blocks per SM: only the most-used slots take shared memory.
-template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0>
+// SEGG > 0 (scene-specialised kernels only): keyed curves are solved from segment records staged in shared memory
+// (stage_issue / stage_wait / curve_staged); SEGG = channels per curve group = records rows of one staging buffer.
+template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0>
 struct Walker {
     static constexpr int NT = OMO_NT;
     static constexpr int TREE = OUT ? 0 : 1;   // 0: every body, 1: candidate-independent subtrees pruned
@@ -39,6 +42,9 @@ struct Walker {
     unsigned short* __restrict__ seg0;  // this warp's segment warm starts, [n_keyed]
     const double* __restrict__ pc;      // this candidate's prepared control points
     int tid, N, tile_end;
+    int item;                   // (candidate, tile) work item of this thread's OMO_NT-thread group
+    bool item_valid;            // false for the padding groups of the last block (OMO_SUB > 1)
+    double* sm0;                // this work item's slice of dynamic shared memory
     size_t dof;
     bool sorted;
     unsigned n_bez, n_newton, n_iksolve, n_ikiter;
@@ -57,6 +63,9 @@ struct Walker {
     SV6 groot;                            // OUT only: force folded into the root
     double ikq[IK ? OMO_MAX_IK * 3 * OMO_MAX_IK_CHAIN : 1];
     double rs[NREG > 0 ? NREG : 1][OMO_SLOT];
+    const double* __restrict__ sgc;   // SEGG > 0: this candidate's segment records
+    double* wsb;                      //           staging buffers [buf][SEGG][OMO_SEGW][OMO_SEGD]
+    int* wbase;                       //           [n_keyed] chain position of each keyed channel's first staged record
 
     __device__ __forceinline__ Walker(const OmoEvalParams& P_) : P(P_) {}
 
@@ -83,12 +92,22 @@ struct Walker {
 
     // ---- block / thread set-up -------------------------------------------------------------------------------------
     // n_smem_slots: stack slots that live in shared memory (the scene's plan, or the specialised kernel's own)
-    __device__ __forceinline__ void begin(double* smem, const int n_smem_slots)
+    __device__ __forceinline__ void begin(double* smem, const int n_smem_slots, const bool stage_in_stack = false)
     {
         const OmoDevScene& S = c_scene;
-        tid = threadIdx.x;
-        const int cand = blockIdx.x / P.n_tiles;
-        const int tile = blockIdx.x - cand * P.n_tiles;
+        if (OMO_SUB > 1) {
+            const int sub = threadIdx.x / NT;
+            tid = threadIdx.x - sub * NT;
+            item = blockIdx.x * OMO_SUB + sub;
+            item_valid = item < P.n_items;
+            item = min(item, P.n_items - 1);
+            smem += (size_t)sub * P.smem_stride;
+        } else {
+            tid = threadIdx.x; item = blockIdx.x; item_valid = true;
+        }
+        sm0 = smem;
+        const int cand = item / P.n_tiles;
+        const int tile = item - cand * P.n_tiles;
         const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);
         ex = smem;
         double* stk0 = smem + ex_rows * NT;
@@ -100,6 +119,24 @@ struct Walker {
         dof = (size_t)3 * S.J;
         n_bez = n_newton = n_iksolve = n_ikiter = 0u;
         xbuf = 0;
+        if (SEGG > 0) {
+            // staged curves: wbase[] and the staging buffers sit behind the stack -- or, when the only curve group opens
+            // the walk (stage_in_stack), in the stack area itself, which no body has touched yet
+            seg0 = nullptr;
+            sgc = P.seg + (size_t)cand * P.n_cp * OMO_SEGD;
+            double* tail = stk0 + (size_t)n_smem_slots * (OMO_SLOT * NT);
+            const int wb_doubles = ((S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double);
+            if (!stage_in_stack) { wbase = reinterpret_cast<int*>(tail); wsb = tail + wb_doubles; }
+            else { wbase = reinterpret_cast<int*>(stk0); wsb = stk0 + wb_doubles; }
+            if (sorted) {
+                const unsigned short* __restrict__ ts = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
+                for (int i = tid; i < S.n_keyed; i += NT) {
+                    const int n = S.chan_n[S.grp_list[i]];
+                    wbase[i] = (n >= 2) ? min(max((int)__ldg(ts + i), 1), n - 1) : 1;
+                }
+            }
+            __syncthreads();
+        } else {
         // seg0[warp][n_keyed] (16-bit) sits behind the stack in dynamic shared memory
         seg0 = reinterpret_cast<unsigned short*>(stk0 + (size_t)n_smem_slots * (OMO_SLOT * NT)) + (tid >> 5) * S.n_keyed;
 
@@ -119,11 +156,12 @@ struct Walker {
             }
         }
         __syncwarp();
+        }
 
         idx = tid;
         const int s_raw = tile * P.T_out - 2 + idx;
         s = min(max(s_raw, 0), N - 1);
-        owned = (idx >= 2) && (s_raw < tile_end) && (s_raw >= 0);
+        owned = (idx >= 2) && (s_raw < tile_end) && (s_raw >= 0) && item_valid;
         interior = (s >= 2) && (s <= N - 3);
         t = __ldg(P.tgrid + s);
         tsq = (!OUT && interior) ? S.static_tsq : 0.0;   // the pruned bodies' share (candidate-independent)
@@ -277,6 +315,71 @@ struct Walker {
     }
     __device__ __forceinline__ void group_sync() { __syncthreads(); }
 
+    // ---- staged sampling (SEGG > 0) ----------------------------------------------------------------------------------
+    // Asynchronous copy (cp.async, 16 B per request) of the OMO_SEGW segment records of each of the nch keyed channels
+    // grp_list[g0 ..] into staging buffer `buf`. Issued one group ahead; stage_wait + the group barrier publish it.
+    __device__ __forceinline__ void stage_issue(const int buf, const int g0, const int nch)
+    {
+        if (SEGG == 0 || !sorted) return;
+        const OmoDevScene& S = c_scene;
+        constexpr int U = OMO_SEGD / 2;   // 16-byte units per record
+        const int items = nch * OMO_SEGW * U;
+        for (int it = tid; it < items; it += NT) {
+            const int lc = it / (OMO_SEGW * U), r = it - lc * (OMO_SEGW * U), j = r / U, u = r - j * U;
+            const int ch = S.grp_list[g0 + lc], base = wbase[g0 + lc];
+            if (base + j <= S.chan_n[ch] - 1) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(wsb + (size_t)((buf * SEGG + lc) * OMO_SEGW + j) * OMO_SEGD + 2 * u);
+                const double* src = sgc + (size_t)(S.chan_pos[ch] + base + j) * OMO_SEGD + 2 * u;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    __device__ __forceinline__ void stage_wait()
+    {
+        if (SEGG > 0) asm volatile("cp.async.wait_all;" ::: "memory");
+    }
+
+    // K (<= 3) keyed joint channels (entries i0.. of grp_list, rows lc0.. of staging buffer buf) sampled in lockstep from
+    // the staged records into the exchange rows
+    template <int K>
+    __device__ __forceinline__ void curve_staged(const int buf, const int i0, const int lc0, const int ch0, const int ch1, const int ch2)
+    {
+        const OmoDevScene& S = c_scene;
+        const int ch[3] = {ch0, ch1, ch2};
+        double val[K];
+        if (!sorted) {   // a key moved past its neighbour: list-order search through global memory, one curve at a time
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                unsigned eb = 0, en = 0;
+                val[k] = COUNT ? eval_channel(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false, eb, en)
+                               : eval_channel_slow(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false);
+                if (COUNT && owned) { n_bez += eb; n_newton += en; }
+            }
+        } else {
+            const double* sk[K];
+            int nn[K], base[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                sk[k] = wsb + (size_t)((buf * SEGG + lc0 + k) * OMO_SEGW) * OMO_SEGD;
+                nn[k] = S.chan_n[ch[k]];
+                base[k] = wbase[i0 + k];
+            }
+            unsigned fb = 0, eb = 0, en = 0;
+            eval_channels_staged<K, COUNT>(sk, nn, base, t, val, fb, eb, en);
+            if (fb) {   // this thread's segment lies beyond the staged window (keys denser than OMO_SEGW per block)
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (fb >> k & 1u)
+                        val[k] = COUNT ? eval_channel(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true, eb, en)
+                                       : eval_channel_slow(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true);
+            }
+            if (COUNT && owned) { n_bez += eb; n_newton += en; }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) ex[S.chan_row[ch[k]] * NT + idx] = val[k];
+    }
+
     // ---- forward step of a joint frozen at zero angles: E = I, qd = qdd = 0 exactly --------------------------------
     __device__ __forceinline__ void body_ident(const int b)
     {
@@ -350,6 +453,94 @@ struct Walker {
         v = vn; a = an;
     }
 
+    // ---- the same steps with the scene's structural zeros resolved at compile time (scene-specialised kernels) ---------
+    // Channel kind Kk of the body's angle k: 0 = keyed (exchange row, stencil, sincos), 1 = constant (sin / cos / stencil
+    // residue from the scene table), 3 = the constant 0 (sin = ZeroT, cos = OneT, qd = qdd = ZeroT). ZB: omo_rnea_z.cuh.
+    template <int KIND> static __device__ __forceinline__ auto zs(const double x) { if constexpr (KIND == 3) return ZeroT{}; else return x; }
+    template <int KIND> static __device__ __forceinline__ auto zc(const double x) { if constexpr (KIND == 3) return OneT{}; else return x; }
+    template <int K0, int K1, int K2>
+    static __device__ __forceinline__ auto make_sc(const double a0, const double b0, const double a1, const double b1, const double a2, const double b2)
+    {
+        return SinCosZ<decltype(zs<K0>(0.0)), decltype(zc<K0>(0.0)), decltype(zs<K1>(0.0)), decltype(zc<K1>(0.0)), decltype(zs<K2>(0.0)),
+                       decltype(zc<K2>(0.0))>{zs<K0>(a0), zc<K0>(b0), zs<K1>(a1), zc<K1>(b1), zs<K2>(a2), zc<K2>(b2)};
+    }
+
+    template <int K0, int K1, int K2, int ZB>
+    __device__ __forceinline__ void body_z(const int b, const int row0, const int row1, const int row2)
+    {
+        const OmoDevScene& S = c_scene;
+        constexpr int kind[3] = {K0, K1, K2};
+        const int rowk[3] = {row0, row1, row2};
+        double qd[3] = {0.0, 0.0, 0.0}, qdd[3] = {0.0, 0.0, 0.0}, ss[3] = {0.0, 0.0, 0.0}, cc[3] = {1.0, 1.0, 1.0};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (kind[k] == 0) {
+                const double* __restrict__ row = ex + rowk[k] * NT;
+                const double m2 = row[max(idx - 2, 0)], m1 = row[max(idx - 1, 0)], x = row[idx];
+                const double p1 = row[min(idx + 1, NT - 1)], p2 = row[min(idx + 2, NT - 1)];
+                if (interior) {
+                    qd[k] = (-p2 + 8.0 * p1 - 8.0 * m1 + m2) * P.inv_12dt;
+                    qdd[k] = (-p2 + 16.0 * p1 - 30.0 * x + 16.0 * m1 - m2) * P.inv_12dt2;
+                } else if (s == 0) {
+                    qd[k] = (p1 - x) * P.inv_dt;
+                    qdd[k] = (p2 - 2.0 * p1 + x) * P.inv_2dt2;
+                } else if (s == N - 1) {
+                    qd[k] = (x - m1) * P.inv_dt;
+                    qdd[k] = (x - 2.0 * m1 + m2) * P.inv_2dt2;
+                } else {
+                    qd[k] = (p1 - m1) * P.inv_2dt;
+                    qdd[k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
+                }
+                sincos_angle(x, &ss[k], &cc[k]);
+            } else if (kind[k] == 1) {
+                ss[k] = S.chan_sin[3 * b + k]; cc[k] = S.chan_cos[3 * b + k];
+                qd[k] = interior ? S.chan_qd[3 * b + k] : 0.0;
+                qdd[k] = interior ? S.chan_qdd[3 * b + k] : 0.0;
+            }
+        }
+        s0 = ss[0]; s1 = ss[1]; s2 = ss[2]; c0 = cc[0]; c1 = cc[1]; c2 = cc[2];
+        const auto sc = make_sc<K0, K1, K2>(ss[0], cc[0], ss[1], cc[1], ss[2], cc[2]);
+        const Vec3Z<decltype(zs<K0>(0.0)), decltype(zs<K1>(0.0)), decltype(zs<K2>(0.0))> vqd{zs<K0>(qd[0]), zs<K1>(qd[1]), zs<K2>(qd[2])},
+            vqdd{zs<K0>(qdd[0]), zs<K1>(qdd[1]), zs<K2>(qdd[2])};
+        SV6 vn, an;
+        rnea_forward_z(BodyZ<ZB>(S.body[b]), sc, vqd, vqdd, v, a, vn, an, f);
+        v = vn; a = an;
+    }
+    // (f, sincos of the KEYED angles) of a body whose subtree opens; constants are re-read from the scene table on the way back
+    template <int K0, int K1, int K2> __device__ __forceinline__ void park_fs_z(const int sl)
+    {
+        st(sl, 0, f.w0); st(sl, 1, f.w1); st(sl, 2, f.w2); st(sl, 3, f.l0); st(sl, 4, f.l1); st(sl, 5, f.l2);
+        if (K0 == 0) { st(sl, 6, s0); st(sl, 7, c0); }
+        if (K1 == 0) { st(sl, 8, s1); st(sl, 9, c1); }
+        if (K2 == 0) { st(sl, 10, s2); st(sl, 11, c2); }
+    }
+    template <int K0, int K1, int K2, int ZB>
+    __device__ __forceinline__ void finalize_z(const int k, const SV6& fk, const double a0, const double b0, const double a1, const double b1,
+                                               const double a2, const double b2)
+    {
+        const OmoDevScene& S = c_scene;
+        double t0, t1, t2;
+        SV6 gn;
+        rnea_backward_z(BodyZ<ZB>(S.body[k]), make_sc<K0, K1, K2>(a0, b0, a1, b1, a2, b2), fk, gn, t0, t1, t2);
+        g = gn;
+        tsq = fma(t0, t0, fma(t1, t1, fma(t2, t2, tsq)));
+    }
+    template <int K0, int K1, int K2, int ZB> __device__ __forceinline__ void fold_leaf_z(const int b)
+    {
+        finalize_z<K0, K1, K2, ZB>(b, f, s0, c0, s1, c1, s2, c2);
+    }
+    template <int K0, int K1, int K2, int ZB> __device__ __forceinline__ void fold_up_z(const int k, const int sl)
+    {
+        const OmoDevScene& S = c_scene;
+        SV6 fk;
+        fk.w0 = ld(sl, 0) + g.w0; fk.w1 = ld(sl, 1) + g.w1; fk.w2 = ld(sl, 2) + g.w2;
+        fk.l0 = ld(sl, 3) + g.l0; fk.l1 = ld(sl, 4) + g.l1; fk.l2 = ld(sl, 5) + g.l2;
+        const double a0 = K0 == 0 ? ld(sl, 6) : (K0 == 1 ? S.chan_sin[3 * k] : 0.0), b0 = K0 == 0 ? ld(sl, 7) : (K0 == 1 ? S.chan_cos[3 * k] : 1.0);
+        const double a1 = K1 == 0 ? ld(sl, 8) : (K1 == 1 ? S.chan_sin[3 * k + 1] : 0.0), b1 = K1 == 0 ? ld(sl, 9) : (K1 == 1 ? S.chan_cos[3 * k + 1] : 1.0);
+        const double a2 = K2 == 0 ? ld(sl, 10) : (K2 == 1 ? S.chan_sin[3 * k + 2] : 0.0), b2 = K2 == 0 ? ld(sl, 11) : (K2 == 1 ? S.chan_cos[3 * k + 2] : 1.0);
+        finalize_z<K0, K1, K2, ZB>(k, fk, a0, b0, a1, b1, a2, b2);
+    }
+
     // ---- forward kinematics: p_b and the world affine handed to b's children (joint.cpp:64-83) --------------------------
     __device__ __forceinline__ void fk_step(const int b, const bool has_child, const bool ident)
     {
@@ -386,8 +577,9 @@ struct Walker {
     }
 
     // ---- cost of the sample and block reduction (local_cost = |tau[3:]|^2 dt, core_rbdl.cpp:331-334) ----------------
-    __device__ __forceinline__ void finish(double* smem)
+    __device__ __forceinline__ void finish(double*)
     {
+        double* smem = sm0;
         double wc = 0.0, wt = 0.0;
         const double local = tsq * P.dt;
         if (OUT && owned) {
@@ -408,11 +600,11 @@ struct Walker {
         double* red = smem;
         if ((tid & 31) == 0) { red[2 * (tid >> 5)] = wc; red[2 * (tid >> 5) + 1] = wt; }
         __syncthreads();
-        if (tid == 0) {
+        if (tid == 0 && item_valid) {
             double C = 0.0, D = 0.0;
             for (int w = 0; w < (NT >> 5); ++w) { C += red[2 * w]; D += red[2 * w + 1]; }
-            P.partial[(size_t)blockIdx.x * 2] = C;
-            P.partial[(size_t)blockIdx.x * 2 + 1] = D;
+            P.partial[(size_t)item * 2] = C;
+            P.partial[(size_t)item * 2 + 1] = D;
         }
         if (COUNT && P.counters) {
             unsigned cb = n_bez, cn = n_newton, ci = n_iksolve, cj = n_ikiter;

@@ -219,3 +219,25 @@ def test_counters_report_executed_curve_and_ik_work():
     assert 12 * 220 <= k["ik_iters"] <= 20 * 220
     assert 0 < k["bezier_evals"] <= 220 * 4 and k["newton_iters"] >= k["bezier_evals"]
     assert k["launches"] > 0
+
+
+def test_hand_scheduled_division_is_ieee_exact():
+    """div_rn_fast (the curve solver's branch-free f / f') == the compiler's IEEE division bit for bit wherever its own
+    validity test passes; operands of the size Newton produces must all pass it."""
+    c = Core(scene_path("stick-figure"))
+    eng = c.engine()
+    rng = np.random.default_rng(7)
+    n = 1 << 20
+    # Newton-like operands, a wide log-uniform sweep, and edge cases (zeros, denormals, infinities, NaN, huge ratios)
+    num = np.concatenate([rng.normal(size=n) * 10.0 ** rng.uniform(-12, 2, n), rng.normal(size=n) * 10.0 ** rng.uniform(-300, 300, n),
+                          np.array([0.0, -0.0, 1.0, 5e-324, 1e-310, np.inf, -np.inf, np.nan, 1e308, 1e-308, 3.0, 1.0])])
+    den = np.concatenate([rng.normal(size=n) * 10.0 ** rng.uniform(-3, 3, n), rng.normal(size=n) * 10.0 ** rng.uniform(-300, 300, n),
+                          np.array([1.0, 1.0, 0.0, 1.0, 3.0, 1.0, np.inf, 1.0, 1e-308, 1e308, 5e-324, 3.0])])
+    qf, qr, ok = eng.selftest_division(num, den)
+    sel = ok != 0
+    assert np.array_equal(qf[sel].view(np.uint64), qr[sel].view(np.uint64))
+    assert sel[:n].all()                       # the Newton-sized operands never need the full-range routine
+    with np.errstate(all="ignore"):
+        host = num / den
+    fin = np.isfinite(host)
+    assert np.array_equal(qr[fin].view(np.uint64), host[fin].view(np.uint64))   # and the device reference is IEEE
