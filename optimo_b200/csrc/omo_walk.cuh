@@ -453,6 +453,24 @@ struct Walker {
         v = vn; a = an;
     }
 
+    // A whole curve group: n3 lockstep triples as ONE loop body (the channel numbers come from grp_list) plus a tail of
+    // `rem` curves. Keeps the code of a 189-curve scene the size of one triple -- the specialised kernel is bound by
+    // instruction supply (profiles/micro/icache_mix), straight-line repetition of the solver is what it cannot afford.
+    template <int REM>
+    __device__ __forceinline__ void curve_group(const int buf, const int g0, const int n3)
+    {
+        const OmoDevScene& S = c_scene;
+#pragma unroll 1
+        for (int c = 0; c < n3; ++c) {
+            const int i0 = g0 + 3 * c;
+            curve_staged<3>(buf, i0, 3 * c, S.grp_list[i0], S.grp_list[i0 + 1], S.grp_list[i0 + 2]);
+        }
+        if (REM > 0) {
+            const int i0 = g0 + 3 * n3;
+            curve_staged<(REM > 0 ? REM : 1)>(buf, i0, 3 * n3, S.grp_list[i0], REM > 1 ? S.grp_list[i0 + 1] : -1, -1);
+        }
+    }
+
     // ---- the same steps with the scene's structural zeros resolved at compile time (scene-specialised kernels) ---------
     // Channel kind Kk of the body's angle k: 0 = keyed (exchange row, stencil, sincos), 1 = constant (sin / cos / stencil
     // residue from the scene table), 3 = the constant 0 (sin = ZeroT, cos = OneT, qd = qdd = ZeroT). ZB: omo_rnea_z.cuh.
