@@ -21,30 +21,41 @@
 
 namespace omo {
 
+// The polynomial / reduction constants live in constant memory: a DFMA takes a constant-bank operand directly, whereas a
+// 64-bit literal costs two UMOVs per use -- ~200 extra issue slots per thread on the stick-figure walk.
+__constant__ double c_sincos[18] = {
+    6.36619772367581382433e-01, 6755399441055744.0,                                        // 0: 2/pi  1: rounding magic
+    1.57079632679489655800e+00, 6.12323399573676603587e-17, -1.49738490485916983692e-33,   // 2-4: pi/2 in three pieces
+    1.58969099521155010221e-10, -2.50507602534068634195e-08, 2.75573137070700676789e-06,   // 5-10: sin kernel S6..S1
+    -1.98412698298579493134e-04, 8.33333333332248946124e-03, -1.66666666666666324348e-01,
+    -1.13596475577881948265e-11, 2.08757232129817482790e-09, -2.75573143513906633035e-07,  // 11-16: cos kernel C6..C1
+    2.48015872894767294178e-05, -1.38888888888741095749e-03, 4.16666666666666019037e-02,
+    1.0e5};
+
 __device__ __forceinline__ void sincos_angle(const double x, double* __restrict__ s_out, double* __restrict__ c_out)
 {
-    if (!(fabs(x) <= 1.0e5)) { sincos(x, s_out, c_out); return; }   // also catches NaN / inf
+    if (!(fabs(x) <= c_sincos[17])) { sincos(x, s_out, c_out); return; }   // also catches NaN / inf
     // k = nearest integer to x * 2/pi (magic-number rounding), r = x - k*pi/2 in three exact-product steps
-    const double t = fma(x, 6.36619772367581382433e-01, 6755399441055744.0);
+    const double t = fma(x, c_sincos[0], c_sincos[1]);
     const int k = __double2loint(t);
-    const double kd = t - 6755399441055744.0;
-    double r = fma(-kd, 1.57079632679489655800e+00, x);     // pi/2 rounded to 53 bits
-    r = fma(-kd, 6.12323399573676603587e-17, r);            // next 53 bits
-    r = fma(-kd, -1.49738490485916983692e-33, r);           // and the next
+    const double kd = t - c_sincos[1];
+    double r = fma(-kd, c_sincos[2], x);     // pi/2 rounded to 53 bits
+    r = fma(-kd, c_sincos[3], r);            // next 53 bits
+    r = fma(-kd, c_sincos[4], r);           // and the next
     const double z = r * r;
     // sin kernel: r + r*z*(S1 + z*(S2 + ... ))
-    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
-    ps = fma(z, ps, 2.75573137070700676789e-06);
-    ps = fma(z, ps, -1.98412698298579493134e-04);
-    ps = fma(z, ps, 8.33333333332248946124e-03);
-    ps = fma(z, ps, -1.66666666666666324348e-01);
+    double ps = fma(z, c_sincos[5], c_sincos[6]);
+    ps = fma(z, ps, c_sincos[7]);
+    ps = fma(z, ps, c_sincos[8]);
+    ps = fma(z, ps, c_sincos[9]);
+    ps = fma(z, ps, c_sincos[10]);
     const double sn = fma(r * z, ps, r);
     // cos kernel: 1 - z/2 + z*z*(C1 + z*(C2 + ...)), evaluated as a + (((1 - a) - hz) + z*rc) with a = 1 - hz
-    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
-    pc = fma(z, pc, -2.75573143513906633035e-07);
-    pc = fma(z, pc, 2.48015872894767294178e-05);
-    pc = fma(z, pc, -1.38888888888741095749e-03);
-    pc = fma(z, pc, 4.16666666666666019037e-02);
+    double pc = fma(z, c_sincos[11], c_sincos[12]);
+    pc = fma(z, pc, c_sincos[13]);
+    pc = fma(z, pc, c_sincos[14]);
+    pc = fma(z, pc, c_sincos[15]);
+    pc = fma(z, pc, c_sincos[16]);
     const double hz = 0.5 * z;
     const double a = 1.0 - hz;
     const double cs = a + (((1.0 - a) - hz) + z * (z * pc));
