@@ -31,7 +31,9 @@ namespace omo {
 // That is how deep trees keep several blocks per SM: only the most-used slots take shared memory.
 // SEGG > 0 (scene-specialised kernels only): keyed curves are solved from segment records staged in shared memory
 // (stage_issue / stage_wait / curve_staged); SEGG = channels per curve group = records rows of one staging buffer.
-template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0>
+// CPT (scene-specialised kernels only): compact stack. A slot argument is then the slot's first ROW of the shared-memory
+// stack (slots are as wide as what is parked in them, 6 to 12 rows), or 4096 + r for per-thread slot r.
+template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0, bool CPT = false>
 struct Walker {
     static constexpr int NT = OMO_NT;
     static constexpr int TREE = OUT ? 0 : 1;   // 0: every body, 1: candidate-independent subtrees pruned
@@ -72,13 +74,13 @@ struct Walker {
     // stack element c of slot sl
     __device__ __forceinline__ double ld(const int sl, const int c) const
     {
-        if (NREG > 0 && sl >= 256) return rs[sl - 256][c];
-        return stk[(size_t)(sl * OMO_SLOT + c) * NT];
+        if (NREG > 0 && sl >= (CPT ? 4096 : 256)) return rs[sl - (CPT ? 4096 : 256)][c];
+        return stk[(size_t)((CPT ? sl : sl * OMO_SLOT) + c) * NT];
     }
     __device__ __forceinline__ void st(const int sl, const int c, const double x)
     {
-        if (NREG > 0 && sl >= 256) rs[sl - 256][c] = x;
-        else stk[(size_t)(sl * OMO_SLOT + c) * NT] = x;
+        if (NREG > 0 && sl >= (CPT ? 4096 : 256)) rs[sl - (CPT ? 4096 : 256)][c] = x;
+        else stk[(size_t)((CPT ? sl : sl * OMO_SLOT) + c) * NT] = x;
     }
 
     // root state (RBDL body 1, TranslationXYZ, q = root offset: core_rbdl.cpp:137-141,212): v = (0, qd), a = (0, qdd)
@@ -91,7 +93,8 @@ struct Walker {
     }
 
     // ---- block / thread set-up -------------------------------------------------------------------------------------
-    // n_smem_slots: stack slots that live in shared memory (the scene's plan, or the specialised kernel's own)
+    // n_smem_slots: stack slots that live in shared memory (the scene's plan, or the specialised kernel's own); with CPT
+    // it is the number of ROWS of the shared-memory stack
     __device__ __forceinline__ void begin(double* smem, const int n_smem_slots, const bool stage_in_stack = false)
     {
         const OmoDevScene& S = c_scene;
@@ -124,7 +127,7 @@ struct Walker {
             // the walk (stage_in_stack), in the stack area itself, which no body has touched yet
             seg0 = nullptr;
             sgc = P.seg + (size_t)cand * P.n_cp * OMO_SEGD;
-            double* tail = stk0 + (size_t)n_smem_slots * (OMO_SLOT * NT);
+            double* tail = stk0 + (size_t)n_smem_slots * ((CPT ? 1 : OMO_SLOT) * NT);
             const int wb_doubles = ((S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double);
             if (!stage_in_stack) { wbase = reinterpret_cast<int*>(tail); wsb = tail + wb_doubles; }
             else { wbase = reinterpret_cast<int*>(stk0); wsb = stk0 + wb_doubles; }
@@ -528,9 +531,11 @@ struct Walker {
     template <int K0, int K1, int K2> __device__ __forceinline__ void park_fs_z(const int sl)
     {
         st(sl, 0, f.w0); st(sl, 1, f.w1); st(sl, 2, f.w2); st(sl, 3, f.l0); st(sl, 4, f.l1); st(sl, 5, f.l2);
+        // keyed angles only, packed behind f: rows 6.., two per keyed channel
+        constexpr int o1 = 6 + (K0 == 0 ? 2 : 0), o2 = o1 + (K1 == 0 ? 2 : 0);
         if (K0 == 0) { st(sl, 6, s0); st(sl, 7, c0); }
-        if (K1 == 0) { st(sl, 8, s1); st(sl, 9, c1); }
-        if (K2 == 0) { st(sl, 10, s2); st(sl, 11, c2); }
+        if (K1 == 0) { st(sl, o1, s1); st(sl, o1 + 1, c1); }
+        if (K2 == 0) { st(sl, o2, s2); st(sl, o2 + 1, c2); }
     }
     template <int K0, int K1, int K2, int ZB>
     __device__ __forceinline__ void finalize_z(const int k, const SV6& fk, const double a0, const double b0, const double a1, const double b1,
@@ -553,9 +558,10 @@ struct Walker {
         SV6 fk;
         fk.w0 = ld(sl, 0) + g.w0; fk.w1 = ld(sl, 1) + g.w1; fk.w2 = ld(sl, 2) + g.w2;
         fk.l0 = ld(sl, 3) + g.l0; fk.l1 = ld(sl, 4) + g.l1; fk.l2 = ld(sl, 5) + g.l2;
+        constexpr int o1 = 6 + (K0 == 0 ? 2 : 0), o2 = o1 + (K1 == 0 ? 2 : 0);
         const double a0 = K0 == 0 ? ld(sl, 6) : (K0 == 1 ? S.chan_sin[3 * k] : 0.0), b0 = K0 == 0 ? ld(sl, 7) : (K0 == 1 ? S.chan_cos[3 * k] : 1.0);
-        const double a1 = K1 == 0 ? ld(sl, 8) : (K1 == 1 ? S.chan_sin[3 * k + 1] : 0.0), b1 = K1 == 0 ? ld(sl, 9) : (K1 == 1 ? S.chan_cos[3 * k + 1] : 1.0);
-        const double a2 = K2 == 0 ? ld(sl, 10) : (K2 == 1 ? S.chan_sin[3 * k + 2] : 0.0), b2 = K2 == 0 ? ld(sl, 11) : (K2 == 1 ? S.chan_cos[3 * k + 2] : 1.0);
+        const double a1 = K1 == 0 ? ld(sl, o1) : (K1 == 1 ? S.chan_sin[3 * k + 1] : 0.0), b1 = K1 == 0 ? ld(sl, o1 + 1) : (K1 == 1 ? S.chan_cos[3 * k + 1] : 1.0);
+        const double a2 = K2 == 0 ? ld(sl, o2) : (K2 == 1 ? S.chan_sin[3 * k + 2] : 0.0), b2 = K2 == 0 ? ld(sl, o2 + 1) : (K2 == 1 ? S.chan_cos[3 * k + 2] : 1.0);
         finalize_z<K0, K1, K2, ZB>(k, fk, a0, b0, a1, b1, a2, b2);
     }
 
