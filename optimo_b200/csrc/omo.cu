@@ -33,6 +33,9 @@ struct omo_ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;      // host -> device copies of omo_eval, pipelined against the kernels on `stream`
+    cudaEvent_t chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t done_ev = nullptr;
     std::string err;
 
     // scene
@@ -560,7 +563,9 @@ omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
     Q.n_cp = ctx->n_cp; Q.D = ctx->D; Q.cyclic = ctx->cyclic;
     Q.seg = ctx->d_seg; Q.tile_seg = ctx->d_tile_seg; Q.tgrid = ctx->d_tgrid;
     Q.N_s = ctx->N_s; Q.T_out = ctx->T_out; Q.n_tiles = ctx->n_tiles; Q.n_keyed = ctx->hs.n_keyed;
-    omo::prepare_kernel<<<B, 128, 0, ctx->stream>>>(Q);
+    const size_t sh = (size_t)6 * ctx->n_cp * sizeof(double);
+    Q.use_smem = sh <= (size_t)40 * 1024 ? 1 : 0;
+    omo::prepare_kernel<<<B, 128, Q.use_smem ? sh : 0, ctx->stream>>>(Q);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return OMO_OK;
@@ -702,6 +707,9 @@ void omo_destroy(omo_ctx* ctx)
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+    for (auto& e : ctx->chunk_ev) if (e) cudaEventDestroy(e);
+    if (ctx->done_ev) cudaEventDestroy(ctx->done_ev);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -832,8 +840,38 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
-    OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, (size_t)B * ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
+    // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
+    // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
+    const size_t bytes = (size_t)B * ctx->D * sizeof(double);
+    const int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(8, std::min<size_t>(bytes / ((size_t)4 << 20), (size_t)B)));
+    if (n_chunks == 1) {
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
+    } else {
+        if (!ctx->copy_stream) {
+            OMO_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+            for (auto& e : ctx->chunk_ev) OMO_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            OMO_CUDA(cudaEventCreateWithFlags(&ctx->done_ev, cudaEventDisableTiming));
+        }
+        // d_X may still be read by kernels queued earlier on `stream`
+        OMO_CUDA(cudaEventRecord(ctx->done_ev, ctx->stream));
+        OMO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->done_ev, 0));
+        const int per = (B + n_chunks - 1) / n_chunks;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b0 = c * per, nb = std::min(per, B - b0);
+            if (nb <= 0) break;
+            OMO_CUDA(cudaMemcpyAsync(ctx->d_X + (size_t)b0 * ctx->D, X + (size_t)b0 * ctx->D, (size_t)nb * ctx->D * sizeof(double),
+                                     cudaMemcpyHostToDevice, ctx->copy_stream));
+            OMO_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
+        }
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b0 = c * per, nb = std::min(per, B - b0);
+            if (nb <= 0) break;
+            OMO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0));
+            if ((st = eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, ctx->d_f + b0, terms_out ? ctx->d_terms + (size_t)3 * b0 : nullptr)) != OMO_OK)
+                return st;
+        }
+    }
     OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
