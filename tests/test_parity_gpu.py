@@ -241,3 +241,66 @@ def test_hand_scheduled_division_is_ieee_exact():
         host = num / den
     fin = np.isfinite(host)
     assert np.array_equal(qr[fin].view(np.uint64), host[fin].view(np.uint64))   # and the device reference is IEEE
+
+
+def _forced(monkeypatch, mode, **env):
+    """A fresh Core whose engine is forced onto (OMO_JIT=1) or off (OMO_JIT=0) the scene-specialised kernel."""
+    monkeypatch.setenv("OMO_JIT", mode)
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+
+
+@pytest.mark.parametrize("form", ["unroll", "loop"])
+def test_specialised_kernel_paths_match_table_driven_kernel(monkeypatch, oracle_port, form):
+    """The scene-specialised kernel (staged segment windows, structural zeros, compact stack; both code forms) against the
+    table-driven kernel and the oracle on the cases that leave its fast path: a candidate with an unsorted chain, a
+    sample window that starts before the first key and ends after the last, keys denser than the staged window
+    (OMO_SEGW segments per 128 samples), a single-key channel, trajectory weight (FK instance) and an IK scene."""
+    cases = []
+    # (a) stick-figure: unsorted chain + out-of-range samples + FK instance
+    scene = load_scene("stick-figure")
+    x0 = Core(scene).GetDescriptor()
+    xa = x0.copy(); xa[0] = 11.5; xa[5 * 7] = 2.0
+    rng = np.random.default_rng(3)
+    xb = x0.copy(); xb[2::5] += 0.2 * (rng.random(xb.size // 5) - 0.5)
+    cases.append((scene, np.stack([xa, xb, x0]), 12.5, (-20.0, 90.0)))
+    # (b) dense keys: a key every frame = 5 samples per segment, 25 segments per block -> every thread beyond the window
+    dense = synthetic.tree_scene(n_joints=6, n_frames=40, key_every=1)
+    xd = Core(dense).GetDescriptor()
+    cases.append((dense, synthetic.perturbed_candidates(xd, 3), 0.0, None))
+    # (c) a single-key channel next to keyed ones
+    single = load_scene("fox-tail")
+    def find(node, name):
+        if node["name"] == name:
+            return node
+        for ch in node.get("children", []):
+            hit = find(ch, name)
+            if hit:
+                return hit
+        return None
+    find(single["joints"], "tail_root")["rot_x"] = {"var": 0.0, "curve": [[12.0, 0.3, 0.1, -1.0, 1.0]]}
+    xs = Core(single).GetDescriptor()
+    cases.append((single, np.stack([xs, xs * 1.0]), 1.0, None))
+    # (d) IK scene
+    cond = load_scene("conductor")
+    xc = Core(cond).GetDescriptor()
+    xc2 = xc.copy(); xc2[2::5] += 0.1 * (rng.random(xc2.size // 5) - 0.5)
+    cases.append((cond, np.stack([xc, xc2]), 12.5, None))
+
+    for scene, X, w_traj, window in cases:
+        res = {}
+        for mode in ("0", "1"):
+            _forced(monkeypatch, mode, OMO_JIT_FORM=form)
+            c = Core(scene)
+            c.UpdateGlobalWeight(w_traj)
+            lo, hi = window if window else c.window
+            x0 = c.GetDescriptor()
+            res[mode] = c.CalculateFullObjectiveBatch(lo, hi, X, x0)
+            if mode == "1":
+                assert c.engine().jit_info()["launches"] > 0, c.engine().jit_info()["log"]
+        assert np.allclose(res["1"], res["0"], rtol=1e-13, atol=0), (res["1"], res["0"])
+        o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1); o.set_weight_trajectory(w_traj)
+        x0 = Core(scene).GetDescriptor()
+        o.update_original(x0)
+        fo, _ = o.full_objective(X[0], x0, window=window) if window else o.full_objective(X[0], x0)
+        assert abs(res["1"][0] - fo) <= TOL * abs(fo) + 1e-15, (res["1"][0], fo)
