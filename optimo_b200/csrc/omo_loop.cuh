@@ -26,7 +26,7 @@ __device__ __forceinline__ void walk_loop(W& w, const short* __restrict__ place)
     int bp = 0;                               // the body visited last (starts at the root)
     int4 mp = S.meta[TREE][0];
     if (S.n_groups > 0) {
-        w.stage_issue(0, S.grp_begin[0], S.grp_begin[1] - S.grp_begin[0]);
+        w.template stage_issue<true>(0, S.grp_begin[0], S.grp_begin[1] - S.grp_begin[0]);
         w.stage_wait();
         w.group_sync();
     }

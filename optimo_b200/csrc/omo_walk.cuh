@@ -68,6 +68,7 @@ struct Walker {
     const double* __restrict__ sgc;   // SEGG > 0: this candidate's segment records
     double* wsb;                      //           staging buffers [buf][SEGG][OMO_SEGW][OMO_SEGD]
     int* wbase;                       //           [n_keyed] chain position of each keyed channel's first staged record
+    const unsigned short* __restrict__ tsg;   //   this (candidate, tile)'s row of the tile table
 
     __device__ __forceinline__ Walker(const OmoEvalParams& P_) : P(P_) {}
 
@@ -131,14 +132,12 @@ struct Walker {
             const int wb_doubles = ((S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double);
             if (!stage_in_stack) { wbase = reinterpret_cast<int*>(tail); wsb = tail + wb_doubles; }
             else { wbase = reinterpret_cast<int*>(stk0); wsb = stk0 + wb_doubles; }
+            // wbase[] is published by the barrier that follows the first stage_issue / stage_wait; that first stage reads
+            // the tile table itself, so the block start is two dependent global round trips deep, not three
+            tsg = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
             if (sorted) {
-                const unsigned short* __restrict__ ts = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
-                for (int i = tid; i < S.n_keyed; i += NT) {
-                    const int n = S.chan_n[S.grp_list[i]];
-                    wbase[i] = (n >= 2) ? min(max((int)__ldg(ts + i), 1), n - 1) : 1;
-                }
+                for (int i = tid; i < S.n_keyed; i += NT) wbase[i] = stage_base(i);
             }
-            __syncthreads();
         } else {
         // seg0[warp][n_keyed] (16-bit) sits behind the stack in dynamic shared memory
         seg0 = reinterpret_cast<unsigned short*>(stk0 + (size_t)n_smem_slots * (OMO_SLOT * NT)) + (tid >> 5) * S.n_keyed;
@@ -321,6 +320,14 @@ struct Walker {
     // ---- staged sampling (SEGG > 0) ----------------------------------------------------------------------------------
     // Asynchronous copy (cp.async, 16 B per request) of the OMO_SEGW segment records of each of the nch keyed channels
     // grp_list[g0 ..] into staging buffer `buf`. Issued one group ahead; stage_wait + the group barrier publish it.
+    // first staged record of keyed channel i: the segment that holds the tile's first sample, clamped into [1, n - 1]
+    __device__ __forceinline__ int stage_base(const int i) const
+    {
+        const int n = c_scene.chan_n[c_scene.grp_list[i]];
+        return (n >= 2) ? min(max((int)__ldg(tsg + i), 1), n - 1) : 1;
+    }
+    // FIRST: the block's first stage -- wbase[] is not visible yet, read the tile table instead
+    template <bool FIRST = false>
     __device__ __forceinline__ void stage_issue(const int buf, const int g0, const int nch)
     {
         if (SEGG == 0 || !sorted) return;
@@ -329,7 +336,7 @@ struct Walker {
         const int items = nch * OMO_SEGW * U;
         for (int it = tid; it < items; it += NT) {
             const int lc = it / (OMO_SEGW * U), r = it - lc * (OMO_SEGW * U), j = r / U, u = r - j * U;
-            const int ch = S.grp_list[g0 + lc], base = wbase[g0 + lc];
+            const int ch = S.grp_list[g0 + lc], base = FIRST ? stage_base(g0 + lc) : wbase[g0 + lc];
             if (base + j <= S.chan_n[ch] - 1) {
                 const unsigned dst = (unsigned)__cvta_generic_to_shared(wsb + (size_t)((buf * SEGG + lc) * OMO_SEGW + j) * OMO_SEGD + 2 * u);
                 const double* src = sgc + (size_t)(S.chan_pos[ch] + base + j) * OMO_SEGD + 2 * u;
