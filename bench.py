@@ -264,7 +264,15 @@ def run_ours(args):
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    alg_bytes = 8.0 * (B * 6 * (D // 5) + 2 * B * ((N_s + 123) // 124))   # prepared control points in, tile partials out
+    n_tiles = (N_s + 123) // 124
+
+    def keyed(node, root=True):
+        own = 0 if root else sum(1 for k in ("rot_x", "rot_y", "rot_z") if node[k].get("curve"))
+        return own + sum(keyed(ch, False) for ch in node.get("children", []))
+    n_keyed = keyed(scene["joints"])
+    # what the objective kernel must move: the prepared segment records (10 doubles per control point) and the tile table in,
+    # the tile partials out. (X itself, 8 D bytes per candidate, is read by prepare_kernel.)
+    alg_bytes = float(B) * (80.0 * (D // 5) + 2.0 * n_tiles * n_keyed + 16.0 * n_tiles)
     traffic = None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed `ncu --set full` capture
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:

@@ -376,6 +376,10 @@ omo_status activate_scene(omo_ctx* ctx)
     return OMO_OK;
 }
 
+// prepare_kernel's split of a candidate's chain positions over blocks
+constexpr int kPrepChunk = 640;
+int prep_parts(const omo_ctx* ctx) { return std::max(1, (ctx->n_cp + kPrepChunk - 1) / kPrepChunk); }
+
 omo_status ensure_capacity(omo_ctx* ctx, int B)
 {
     if (B <= ctx->cap) return OMO_OK;
@@ -383,7 +387,7 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
     omo_status st;
     if ((st = dev_alloc(ctx, &ctx->d_X, (size_t)cap * ctx->D)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_prep, (size_t)cap * 6 * ctx->n_cp)) != OMO_OK) return st;
-    if ((st = dev_alloc(ctx, &ctx->d_dparam, (size_t)cap)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_dparam, (size_t)cap * prep_parts(ctx))) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_flags, (size_t)cap)) != OMO_OK) return st;
     // + OMO_SEGW records of slack: the staging copy of the last channel never reads past the allocation
     if ((st = dev_alloc(ctx, &ctx->d_seg, ((size_t)cap * ctx->n_cp + OMO_SEGW) * OMO_SEGD)) != OMO_OK) return st;
@@ -524,7 +528,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     if (!out && mode != 0 && (mode == 1 || (long long)B * ctx->N_s >= 65536)) {
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
-            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, d_f, d_terms);
+            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
             OMO_CUDA(cudaGetLastError());
             ctx->launches += 1;
             return OMO_OK;
@@ -536,7 +540,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     else if (fk) st = count ? launch_objective_t<true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false>(ctx, P, B, plan);
     else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
     if (st != OMO_OK) return st;
-    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, d_f, d_terms);
+    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return OMO_OK;
@@ -563,9 +567,10 @@ omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
     Q.n_cp = ctx->n_cp; Q.D = ctx->D; Q.cyclic = ctx->cyclic;
     Q.seg = ctx->d_seg; Q.tile_seg = ctx->d_tile_seg; Q.tgrid = ctx->d_tgrid;
     Q.N_s = ctx->N_s; Q.T_out = ctx->T_out; Q.n_tiles = ctx->n_tiles; Q.n_keyed = ctx->hs.n_keyed;
-    const size_t sh = (size_t)6 * ctx->n_cp * sizeof(double);
-    Q.use_smem = sh <= (size_t)40 * 1024 ? 1 : 0;
-    omo::prepare_kernel<<<B, 128, Q.use_smem ? sh : 0, ctx->stream>>>(Q);
+    Q.chunk = std::min(kPrepChunk, std::max(ctx->n_cp, 1));
+    const size_t sh = (size_t)6 * (Q.chunk + 1) * sizeof(double);
+    OMO_CUDA(cudaMemsetAsync(ctx->d_flags, 1, (size_t)B * sizeof(unsigned), ctx->stream));   // bit 0 of every word: "sorted"
+    omo::prepare_kernel<<<dim3((unsigned)B, (unsigned)prep_parts(ctx)), 128, sh, ctx->stream>>>(Q);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return OMO_OK;
@@ -843,7 +848,9 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
     // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
     const size_t bytes = (size_t)B * ctx->D * sizeof(double);
-    const int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(8, std::min<size_t>(bytes / ((size_t)4 << 20), (size_t)B)));
+    // a chunk is at least 4 MB and at least ~8 waves of objective blocks
+    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 4736;
+    const int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(8, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));
     if (n_chunks == 1) {
         OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
         if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
