@@ -165,7 +165,8 @@ def run_ours(args):
         for k, i in enumerate(idx):
             X[2 * k + 1, i] += 1e-4
             X[2 * k + 2, i] -= 1e-4
-        desc = f"one objective+gradient evaluation = {B} finite-difference columns of the stick-figure x 240 frames scene"
+        desc = (f"one objective+gradient evaluation = {B} finite-difference columns of the stick-figure x 240 frames scene, "
+                "through omo_eval_grad_columns (columns evaluated only on the tiles their control point reaches; value = executed sample-evals/s)")
     else:
         X = synthetic.perturbed_candidates(x0, B, first=rank * B)
 
@@ -179,13 +180,22 @@ def run_ours(args):
     Fp = eng.pinned_array((B,))
     eng.h2d(dX.data_ptr(), X)
 
+    grad = args.workload == "grad"
+
     def step_device():
-        eng.eval_device(dX.data_ptr(), B, dF.data_ptr(), None, sync=False)
+        if grad:   # the finite-difference columns through the API: built on the device, sparse over tiles (include/omo.h)
+            eng.eval_grad_columns(x_base, idx, 1e-4, 0, B, dF.data_ptr(), sync=False)
+        else:
+            eng.eval_device(dX.data_ptr(), B, dF.data_ptr(), None, sync=False)
         if world > 1:
             dist.all_gather_into_tensor(dAll, dF)
 
     def step_e2e():
-        eng.eval_host_ptr(Xp.ctypes.data, B, Fp.ctypes.data)     # H2D of X, kernels, D2H of f, all inside
+        if grad:   # host x in, (f0, gradient) out on the host
+            g0 = eng.eval_grad(x_base, idx, 1e-4)
+            Fp[0] = g0[0]; Fp[1::2] = g0[2][:, 0]; Fp[2::2] = g0[2][:, 1]
+        else:
+            eng.eval_host_ptr(Xp.ctypes.data, B, Fp.ctypes.data)     # H2D of X, kernels, D2H of f, all inside
         if world > 1:
             dist.barrier()
 
@@ -247,6 +257,10 @@ def run_ours(args):
     cnt = eng.counters()
     eng.set_counting(False)
     n_se = B * N_s
+    executed_frac = 1.0
+    if grad:   # SURVEY.md section 8(d) dense counting rule: report the sample-evals actually executed
+        ex_items, dense_items = eng.grad_sparsity()
+        executed_frac = ex_items / max(dense_items, 1)
     bez, newt = cnt["bezier_evals"] / n_se, cnt["newton_iters"] / n_se
     # SURVEY.md section 8(d) formula. `flops_reference_work` counts all J-1 bodies (what the reference executes per
     # sample); `flops_executed` counts only the bodies the batch kernel walks (candidate-independent subtrees are
@@ -256,7 +270,7 @@ def run_ours(args):
     flops_se = synthetic.flops_per_sample_eval(walked + 1, bez, newt)
     dfma_peak = eng.dfma_peak()                                  # measured in this run: MEASURED_PEAKS.json has no FP64 figure
     k_ms_per_launch = k_ms / max(k_n, 1)
-    achieved = n_se * flops_se / (k_ms_per_launch * 1e-3)
+    achieved = n_se * executed_frac * flops_se / (k_ms_per_launch * 1e-3)
     peaks = {}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -307,7 +321,7 @@ def run_ours(args):
                "sample": f"first {sample} of {B} candidates, candidate-parallel over {leg['cores']} host threads, {leg['seconds']:.2f} s",
                "max_rel_diff_vs_gpu": float(rel)}
 
-    n_total = n_se * world
+    n_total = n_se * executed_frac * world
     value = n_total / (ms_dev * 1e-3)
     e2e_value = n_total / (ms_e2e * 1e-3)
     line = {
@@ -316,9 +330,10 @@ def run_ours(args):
         "config": {"workload": desc, "candidates_per_gpu": B, "samples_per_candidate": N_s, "joints": J, "descriptor": D,
                    "l2": "flushed between timed iterations (256 MiB memset)", "gather": "nccl all_gather of f" if world > 1 else "none"},
         "clocks": sampler.summary() if sampler else None,
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(B * D * 8), "d2h_bytes_per_step": int(B * 8)},
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int((D + 4 * idx.size) if grad else B * D * 8), "d2h_bytes_per_step": int(B * 8)},
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu,
+        "executed_fraction_of_dense_sample_evals": executed_frac,
         "objective_evals_per_s": B * world / (ms_dev * 1e-3), "frame_evals_per_s": value / 5.0,
         "objective_plus_gradient_evals_per_s": (world / (ms_dev * 1e-3)) if args.workload == "grad" else (B * world / (2 * idx.size + 1)) / (ms_dev * 1e-3),
         "wall_s": {"device_loop": wall_dev, "e2e_loop": wall_e2e},

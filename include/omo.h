@@ -144,6 +144,11 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
 omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin,
                                  int col_count, double* d_f_cols, int sync);
 /* grad_k = (cols[2k+1] - cols[2k+2]) / (2h) on the host, from the gathered 2F+1 column values. */
+/* Work actually executed by the last omo_eval_grad / omo_eval_grad_columns call: a finite-difference column moves one control
+ * point, so only the (column, tile) work items whose samples can see it are evaluated and the rest of each sum is taken from
+ * the base point (bit-identical to evaluating every column on every tile; OMO_GRAD_DENSE=1 forces that). out2[0] = work items
+ * executed (tiles of 124 samples, base row included), out2[1] = columns x tiles of the dense evaluation. */
+omo_status omo_grad_sparsity(const omo_ctx* ctx, unsigned long long* out2);
 omo_status omo_grad_from_columns(const double* f_cols, int F, double h, double* f0_out, double* grad_out);
 
 /* Contiguous shard [begin, begin+count) of n items for `rank` of `world` (first ranks take the remainder). */

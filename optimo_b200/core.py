@@ -137,6 +137,7 @@ _OMO_SIG = {
     "omo_measure_dfma_peak": (ci, [_vp, _dp]),
     "omo_jit_info": (ci, [_vp, C.POINTER(_ull), cs, ci]),
     "omo_selftest_division": (ci, [_vp, _dp, _dp, ci, _dp, _dp, _ip]),
+    "omo_grad_sparsity": (ci, [_vp, C.POINTER(_ull)]),
 }
 for _n, (_r, _a) in _OMO_SIG.items():
     _sig(_omo, _n, _r, _a)
@@ -307,6 +308,12 @@ class Engine:
         self._ck(_omo.omo_selftest_division(self.h, num.ctypes.data_as(_dp), den.ctypes.data_as(_dp), n, qf.ctypes.data_as(_dp),
                                             qr.ctypes.data_as(_dp), ok.ctypes.data_as(_ip)), "omo_selftest_division")
         return qf, qr, ok
+
+    def grad_sparsity(self):
+        """(work items executed, work items of the dense evaluation) of the last finite-difference call."""
+        out = (_ull * 2)()
+        self._ck(_omo.omo_grad_sparsity(self.h, out), "omo_grad_sparsity")
+        return int(out[0]), int(out[1])
 
     def dfma_peak(self):
         v = C.c_double(0.0)

@@ -100,6 +100,11 @@ struct omo_ctx {
     int out_cap_samples = 0;
     // gradient scratch
     double* d_xbase = nullptr; int* d_free = nullptr; int free_cap = 0;
+    std::vector<int> pos_of_cp;                 // inverse of cp_of_pos
+    std::vector<int> h_items, h_lo, h_hi;       // sparse finite-difference columns: listed (row, tile) items, tile range per column
+    int *d_items = nullptr, *d_lohi = nullptr;  // their device copies (d_lohi = lo[cols] then hi[cols])
+    size_t items_cap = 0, lohi_cap = 0;
+    unsigned long long sparse_items = 0, dense_items = 0;   // executed / dense work items of the last sparse launch
     std::vector<double> h_cols;
 
     // counters / timing
@@ -432,7 +437,7 @@ omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B, const
         OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
-    omo::objective_kernel<FK, IK, OUT, COUNT><<<B * plan.n_tiles, kBlockThreads, plan.smem, ctx->stream>>>(P);
+    omo::objective_kernel<FK, IK, OUT, COUNT><<<P.n_items, kBlockThreads, plan.smem, ctx->stream>>>(P);
     OMO_CUDA(cudaGetLastError());
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1;
@@ -502,10 +507,9 @@ omo_status launch_jit(omo_ctx* ctx, omo_ctx::JitKernel* k, const OmoEvalParams& 
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
     OmoEvalParams Pc = P;
-    Pc.n_items = B * n_tiles;
     Pc.smem_stride = (int)(k->item_smem / sizeof(double));
     void* args[] = {&Pc};
-    const int rc = a.cuLaunchKernel(k->fn, (unsigned)((B * n_tiles + k->sub - 1) / k->sub), 1, 1, kBlockThreads * k->sub, 1, 1, (unsigned)k->smem,
+    const int rc = a.cuLaunchKernel(k->fn, (unsigned)((Pc.n_items + k->sub - 1) / k->sub), 1, 1, kBlockThreads * k->sub, 1, 1, (unsigned)k->smem,
                                     reinterpret_cast<omo_jit::CUstream>(ctx->stream), args, nullptr);
     if (rc != 0) return fail(ctx, OMO_CUDA_ERROR, "cuLaunchKernel(omo_jit_kernel) failed with CUresult " + std::to_string(rc));
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
@@ -515,19 +519,25 @@ omo_status launch_jit(omo_ctx* ctx, omo_ctx::JitKernel* k, const OmoEvalParams& 
 }
 
 // Launches the objective kernel over B candidates and the finish kernel that adds the tile partials.
-omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool out, double* d_f, double* d_terms)
+// d_item_map (optional): the launch covers only the n_items listed (candidate, tile) pairs and leaves the sums to the caller.
+omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool out, double* d_f, double* d_terms,
+                            const int* d_item_map = nullptr, int n_items = -1)
 {
     const bool ik = ctx->n_ik > 0;
     if (ik || out) fk = true;
     const bool count = P.counters != nullptr && !out;
     const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
-    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.n_items = B * plan.n_tiles; P.smem_stride = 0;
+    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.smem_stride = 0;
+    P.item_map = d_item_map;
+    P.n_items = d_item_map ? n_items : B * plan.n_tiles;
     omo_status st;
     // large launches run the scene-specialised kernel (auto: >= 64 K sample-evals; OMO_JIT=1 always, OMO_JIT=0 never)
     const int mode = jit_mode(ctx);
-    if (!out && mode != 0 && (mode == 1 || (long long)B * ctx->N_s >= 65536)) {
+    // (sparse column launches always do: a gradient's columns must not switch kernels with the size of a rank's shard)
+    if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || (long long)P.n_items * plan.t_out >= 65536)) {
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
+            if (d_item_map) return OMO_OK;
             omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
             OMO_CUDA(cudaGetLastError());
             ctx->launches += 1;
@@ -540,6 +550,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     else if (fk) st = count ? launch_objective_t<true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false>(ctx, P, B, plan);
     else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
     if (st != OMO_OK) return st;
+    if (d_item_map) return OMO_OK;
     omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
@@ -650,6 +661,51 @@ omo_status ensure_ready(omo_ctx* ctx)
     return activate_scene(ctx);
 }
 
+// Sparse finite-difference columns. Fills h_lo / h_hi (tile range each of the columns [col_begin, col_begin + col_count)
+// must be evaluated on; lo > hi = none) and h_items (row * n_tiles + tile for those tiles, then every tile of the extra base
+// row `col_count`). A control point at chain position pos shapes the segments pos-1 -> pos and pos -> pos+1 of its channel
+// (curve.cpp:57-93: each segment reads its two end points only; before the first / after the last key the end value holds),
+// so a sample is affected iff T[pos-1] <= t < T[pos+1] (open ends at a channel's first / last point), and through the
+// 5-point stencils (core_rbdl.cpp:28-95) so are its +-2 neighbours. Returns false -- evaluate densely -- when that
+// reasoning does not hold: a chain of x is not time-sorted (list-order segment search), the perturbed field is the key
+// time itself, or a cyclic curve's end tangents are averaged.
+bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, int col_begin, int col_count)
+{
+    const int n_cp = ctx->n_cp, N = ctx->N_s, T_out = ctx->T_out, n_tiles = ctx->n_tiles;
+    if (n_cp == 0 || N < 5 || n_tiles < 2) return false;
+    if (ctx->pos_of_cp.size() != (size_t)n_cp) {
+        ctx->pos_of_cp.assign(n_cp, 0);
+        for (int pos = 0; pos < n_cp; ++pos) ctx->pos_of_cp[ctx->cp_of_pos[pos]] = pos;
+    }
+    for (int pos = 0; pos + 1 < n_cp; ++pos)
+        if (ctx->next_same[pos] && !(x[5 * ctx->cp_of_pos[pos]] <= x[5 * ctx->cp_of_pos[pos + 1]])) return false;
+    ctx->h_lo.assign(col_count, 0); ctx->h_hi.assign(col_count, n_tiles - 1);
+    ctx->h_items.clear();
+    const std::vector<double>& tg = ctx->tgrid;
+    for (int lc = 0; lc < col_count; ++lc) {
+        const int col = col_begin + lc;
+        int lo = 0, hi = n_tiles - 1;
+        if (col > 0) {
+            const int idx = free_idx[(col - 1) >> 1], cp = idx / 5, field = idx % 5, pos = ctx->pos_of_cp[cp];
+            const bool cyc_end = ctx->cyclic && field == 2 && (cp == ctx->first_of_pos[pos] || cp == ctx->last_of_pos[pos]);
+            if (field == 0 || cyc_end) return false;
+            const double t_lo = (pos > 0 && ctx->next_same[pos - 1]) ? x[5 * ctx->cp_of_pos[pos - 1]] : -INFINITY;
+            const double t_hi = ctx->next_same[pos] ? x[5 * ctx->cp_of_pos[pos + 1]] : INFINITY;
+            // samples with t_lo <= t <= t_hi, one sample of slack each side, then the stencil's two
+            const int s_lo = (int)(std::lower_bound(tg.begin(), tg.end(), t_lo) - tg.begin()) - 3;
+            const int s_hi = (int)(std::upper_bound(tg.begin(), tg.end(), t_hi) - tg.begin()) - 1 + 3;
+            if (s_hi < 0 || s_lo > N - 1) { lo = 1; hi = 0; }
+            else { lo = std::max(s_lo, 0) / T_out; hi = std::min(std::min(s_hi, N - 1) / T_out, n_tiles - 1); }
+        }
+        ctx->h_lo[lc] = lo; ctx->h_hi[lc] = hi;
+        for (int t = lo; t <= hi; ++t) ctx->h_items.push_back(lc * n_tiles + t);
+    }
+    for (int t = 0; t < n_tiles; ++t) ctx->h_items.push_back(col_count * n_tiles + t);
+    ctx->sparse_items = ctx->h_items.size();
+    ctx->dense_items = (unsigned long long)col_count * n_tiles;
+    return true;
+}
+
 omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, double* d_terms)
 {
     omo_status st;
@@ -708,7 +764,7 @@ void omo_destroy(omo_ctx* ctx)
     }
     void* ptrs[] = {ctx->d_cp_of_pos, ctx->d_first_of_pos, ctx->d_last_of_pos, ctx->d_next_same, ctx->d_tgrid, ctx->d_wparam, ctx->d_wcost,
                     ctx->d_x0, ctx->d_p_orig, ctx->d_X, ctx->d_prep, ctx->d_dparam, ctx->d_partial, ctx->d_f, ctx->d_terms, ctx->d_flags,
-                    ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters, ctx->d_seg, ctx->d_tile_seg};
+                    ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_olocal, ctx->d_op, ctx->d_xbase, ctx->d_free, ctx->d_counters, ctx->d_seg, ctx->d_tile_seg, ctx->d_items, ctx->d_lohi};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -933,10 +989,41 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; }
     OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     if (F > 0) OMO_CUDA(cudaMemcpyAsync(ctx->d_free, free_idx, (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-    omo::perturb_kernel<<<col_count, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
+    // Sparse columns: column 2k+1 / 2k+2 moves ONE control point, which only the samples inside its two adjacent segments
+    // (plus the stencil's +-2) can see. Only the tiles holding those samples are evaluated; the sums take every other
+    // tile from the base point, evaluated once as an extra row. Bit-identical to the dense evaluation of every column.
+    const bool sparse = std::getenv("OMO_GRAD_DENSE") == nullptr && affected_tiles(ctx, x, free_idx, F, col_begin, col_count);
+    const int rows = sparse ? col_count + 1 : col_count;
+    if (sparse && (st = ensure_capacity(ctx, rows)) != OMO_OK) return st;
+    omo::perturb_kernel<<<rows, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
-    if ((st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr)) != OMO_OK) return st;
+    if (!sparse) {
+        if ((st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr)) != OMO_OK) return st;
+    } else {
+        if (ctx->h_items.size() > ctx->items_cap) {
+            if ((st = dev_alloc(ctx, &ctx->d_items, ctx->h_items.size())) != OMO_OK) return st;
+            ctx->items_cap = ctx->h_items.size();
+        }
+        if ((size_t)2 * col_count > ctx->lohi_cap) {
+            if ((st = dev_alloc(ctx, &ctx->d_lohi, (size_t)2 * col_count)) != OMO_OK) return st;
+            ctx->lohi_cap = (size_t)2 * col_count;
+        }
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_items, ctx->h_items.data(), ctx->h_items.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi, ctx->h_lo.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi + col_count, ctx->h_hi.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        if ((st = run_prepare(ctx, ctx->d_X, rows)) != OMO_OK) return st;
+        OmoEvalParams P;
+        fill_params(ctx, P);
+        const bool fk = (ctx->w_traj != 0.0) || ctx->n_ik > 0;
+        P.p_orig = (ctx->w_traj != 0.0) ? ctx->d_p_orig : nullptr;
+        if ((st = launch_objective(ctx, P, rows, fk, false, nullptr, nullptr, ctx->d_items, (int)ctx->h_items.size())) != OMO_OK) return st;
+        omo::finish_sparse_kernel<<<(col_count + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, col_count, ctx->n_tiles, prep_parts(ctx),
+                                                                                    ctx->d_lohi, ctx->d_lohi + col_count, col_count, d_f_cols);
+        OMO_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // h_items / h_lo / h_hi are pageable and reused by the next call
+    }
     if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
     return OMO_OK;
 }
@@ -955,13 +1042,20 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     const int P = 2 * F + 1;
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
-    if ((st = ensure_capacity(ctx, P)) != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, P + 1)) != OMO_OK) return st;   // + the base row of the sparse evaluation: d_f must not move below
     if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
     ctx->h_cols.resize(P);
     OMO_CUDA(cudaMemcpyAsync(ctx->h_cols.data(), ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
     if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
     return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
+}
+
+omo_status omo_grad_sparsity(const omo_ctx* ctx, unsigned long long* out2)
+{
+    if (!ctx || !out2) return OMO_BAD_ARG;
+    out2[0] = ctx->sparse_items; out2[1] = ctx->dense_items;
+    return OMO_OK;
 }
 
 void omo_shard_range(int n, int rank, int world, int* begin, int* count)

@@ -103,7 +103,8 @@ struct OmoEvalParams {
     const double* seg;      // [B][n_cp][OMO_SEGD] prepared segments, chain order
     const unsigned short* tile_seg;  // [B][n_tiles][n_keyed] number of keys with time <= the tile's first sample time
     int N_s, n_tiles, T_out, n_cp;
-    int n_items;      // B * n_tiles work items (one per OMO_NT threads)
+    const int* item_map;  // null: work item i is (candidate, tile) number i; else item_map[i] = candidate * n_tiles + tile
+    int n_items;      // work items of this launch (one per OMO_NT threads); B * n_tiles without an item_map
     int smem_stride;  // doubles of dynamic shared memory per work item (used when OMO_SUB > 1)
     double dt, inv_dt, inv_2dt, inv_12dt, inv_dt2, inv_2dt2, inv_12dt2;
     double w_traj;

@@ -110,6 +110,7 @@ struct Walker {
             tid = threadIdx.x; item = blockIdx.x; item_valid = true;
         }
         sm0 = smem;
+        if (P.item_map) item = __ldg(P.item_map + item);   // sparse launches (finite-difference columns): listed (candidate, tile) pairs only
         const int cand = item / P.n_tiles;
         const int tile = item - cand * P.n_tiles;
         const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);

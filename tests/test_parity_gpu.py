@@ -304,3 +304,31 @@ def test_specialised_kernel_paths_match_table_driven_kernel(monkeypatch, oracle_
         o.update_original(x0)
         fo, _ = o.full_objective(X[0], x0, window=window) if window else o.full_objective(X[0], x0)
         assert abs(res["1"][0] - fo) <= TOL * abs(fo) + 1e-15, (res["1"][0], fo)
+
+
+@pytest.mark.parametrize("name", ["stick-figure", "conductor", "stick240"])
+def test_sparse_gradient_columns_equal_dense_evaluation(monkeypatch, name):
+    """Finite-difference columns evaluated only on the tiles their control point can reach (include/omo.h:
+    omo_grad_sparsity) give bit for bit the f(x +- h e_k) of evaluating every column on every sample."""
+    scene = synthetic.stick_240(load_scene("stick-figure")) if name == "stick240" else load_scene(name)
+    res = {}
+    monkeypatch.setenv("OMO_JIT", "1")     # both ways through the scene-specialised kernel (sparse launches always use it)
+    for dense in ("1", None):
+        if dense:
+            monkeypatch.setenv("OMO_GRAD_DENSE", dense)
+        else:
+            monkeypatch.delenv("OMO_GRAD_DENSE", raising=False)
+        c = Core(scene)
+        c.UpdateGlobalWeight(12.5)
+        x0 = c.GetDescriptor()
+        rng = np.random.default_rng(11)
+        x = x0.copy(); x[2::5] += 0.2 * (rng.random(x.size // 5) - 0.5)
+        lo, hi = c.window
+        f0, g, fpm = c.CalculateGradient(lo, hi, x, x0)
+        res[dense] = (f0, g, fpm, c.engine().grad_sparsity())
+    assert res[None][0] == res["1"][0]
+    assert np.array_equal(res[None][2], res["1"][2]) and np.array_equal(res[None][1], res["1"][1])
+    executed, dense_items = res[None][3]
+    assert 0 < executed
+    if name == "stick240":
+        assert executed < dense_items / 3      # 10 tiles per column, one or two of them within reach of a control point
