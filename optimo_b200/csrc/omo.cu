@@ -105,6 +105,10 @@ struct omo_ctx {
     int *d_items = nullptr, *d_lohi = nullptr;  // their device copies (d_lohi = lo[cols] then hi[cols])
     size_t items_cap = 0, lohi_cap = 0;
     unsigned long long sparse_items = 0, dense_items = 0;   // executed / dense work items of the last sparse launch
+    // what the device copies of h_items / h_lo / h_hi / free_idx were built from (an optimisation loop moves theta / t_b / t_f
+    // but no key time, so the item list of one gradient is the next one's too)
+    std::vector<double> sp_times; std::vector<int> sp_free; int sp_begin = -1, sp_count = -1; bool sp_valid = false, sp_uploaded = false;
+    std::vector<int> free_uploaded;
     std::vector<double> h_cols;
 
     // counters / timing
@@ -677,6 +681,13 @@ bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, i
         ctx->pos_of_cp.assign(n_cp, 0);
         for (int pos = 0; pos < n_cp; ++pos) ctx->pos_of_cp[ctx->cp_of_pos[pos]] = pos;
     }
+    {
+        bool same = ctx->sp_valid && ctx->sp_begin == col_begin && ctx->sp_count == col_count && ctx->sp_free.size() == (size_t)F &&
+                    std::equal(ctx->sp_free.begin(), ctx->sp_free.end(), free_idx);
+        for (int pos = 0; same && pos < n_cp; ++pos) same = ctx->sp_times[pos] == x[5 * ctx->cp_of_pos[pos]];
+        if (same) return true;   // device copies are current (sp_uploaded)
+    }
+    ctx->sp_valid = false; ctx->sp_uploaded = false;
     for (int pos = 0; pos + 1 < n_cp; ++pos)
         if (ctx->next_same[pos] && !(x[5 * ctx->cp_of_pos[pos]] <= x[5 * ctx->cp_of_pos[pos + 1]])) return false;
     ctx->h_lo.assign(col_count, 0); ctx->h_hi.assign(col_count, n_tiles - 1);
@@ -703,6 +714,10 @@ bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, i
     for (int t = 0; t < n_tiles; ++t) ctx->h_items.push_back(col_count * n_tiles + t);
     ctx->sparse_items = ctx->h_items.size();
     ctx->dense_items = (unsigned long long)col_count * n_tiles;
+    ctx->sp_times.resize(n_cp);
+    for (int pos = 0; pos < n_cp; ++pos) ctx->sp_times[pos] = x[5 * ctx->cp_of_pos[pos]];
+    ctx->sp_free.assign(free_idx, free_idx + F);
+    ctx->sp_begin = col_begin; ctx->sp_count = col_count; ctx->sp_valid = true;
     return true;
 }
 
@@ -799,6 +814,7 @@ omo_status omo_set_window(omo_ctx* ctx, double min_t, double max_t, double dt)
     refresh_residues(ctx);
     ctx->have_window = true;
     ctx->wcost_dirty = true; ctx->p_orig_dirty = true;
+    ctx->sp_valid = false;  // the sparse-gradient item lists are per time grid
     ctx->cap = 0;  // partial[] depends on n_tiles
     ctx->out_cap_samples = 0;
     return OMO_OK;
@@ -821,6 +837,7 @@ omo_status omo_set_weights(omo_ctx* ctx, const double* w_param, int D, double w_
         same_k = kernels[i].amp == ctx->kernels[i].amp && kernels[i].mu == ctx->kernels[i].mu && kernels[i].sigma == ctx->kernels[i].sigma;
     if (!same_k) { ctx->kernels.assign(kernels, kernels + n_kernels); ctx->wcost_dirty = true; }
     ctx->w_traj = w_traj;
+    if (ctx->cyclic != (cyclic ? 1 : 0)) ctx->sp_valid = false;   // cyclic curves average their end tangents: different reach
     ctx->cyclic = cyclic ? 1 : 0;
     ctx->have_weights = true;
     return OMO_OK;
@@ -986,9 +1003,13 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, col_count)) != OMO_OK) return st;
     if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
-    if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; }
+    if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; ctx->free_uploaded.clear(); }
     OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    if (F > 0) OMO_CUDA(cudaMemcpyAsync(ctx->d_free, free_idx, (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    if (F > 0 && (ctx->free_uploaded.size() != (size_t)F || !std::equal(ctx->free_uploaded.begin(), ctx->free_uploaded.end(), free_idx))) {
+        ctx->free_uploaded.assign(free_idx, free_idx + F);
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_free, ctx->free_uploaded.data(), (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
     // Sparse columns: column 2k+1 / 2k+2 moves ONE control point, which only the samples inside its two adjacent segments
     // (plus the stencil's +-2) can see. Only the tiles holding those samples are evaluated; the sums take every other
     // tile from the base point, evaluated once as an extra row. Bit-identical to the dense evaluation of every column.
@@ -1003,15 +1024,19 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     } else {
         if (ctx->h_items.size() > ctx->items_cap) {
             if ((st = dev_alloc(ctx, &ctx->d_items, ctx->h_items.size())) != OMO_OK) return st;
-            ctx->items_cap = ctx->h_items.size();
+            ctx->items_cap = ctx->h_items.size(); ctx->sp_uploaded = false;
         }
         if ((size_t)2 * col_count > ctx->lohi_cap) {
             if ((st = dev_alloc(ctx, &ctx->d_lohi, (size_t)2 * col_count)) != OMO_OK) return st;
-            ctx->lohi_cap = (size_t)2 * col_count;
+            ctx->lohi_cap = (size_t)2 * col_count; ctx->sp_uploaded = false;
         }
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_items, ctx->h_items.data(), ctx->h_items.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi, ctx->h_lo.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi + col_count, ctx->h_hi.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        if (!ctx->sp_uploaded) {
+            OMO_CUDA(cudaMemcpyAsync(ctx->d_items, ctx->h_items.data(), ctx->h_items.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+            OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi, ctx->h_lo.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+            OMO_CUDA(cudaMemcpyAsync(ctx->d_lohi + col_count, ctx->h_hi.data(), (size_t)col_count * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+            OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // the host vectors are pageable
+            ctx->sp_uploaded = true;
+        }
         if ((st = run_prepare(ctx, ctx->d_X, rows)) != OMO_OK) return st;
         OmoEvalParams P;
         fill_params(ctx, P);
@@ -1022,7 +1047,6 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
                                                                                     ctx->d_lohi, ctx->d_lohi + col_count, col_count, d_f_cols);
         OMO_CUDA(cudaGetLastError());
         ctx->launches += 1;
-        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // h_items / h_lo / h_hi are pageable and reused by the next call
     }
     if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
     return OMO_OK;
