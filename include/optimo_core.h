@@ -70,6 +70,10 @@ int optimo_evaluate_objective(void* h, const double* x_free, int n_free, const d
 void optimo_set_stop_optimization(void* h, int flag);     /* Core::stop_optimization_ */
 int optimo_get_stop_optimization(void* h);
 int optimo_perform_optimization(void* h, int explicit_termination, double* final_value, int* evals);  /* core_opt.cpp:60-157 */
+/* The same solve with a gradient-based NLopt algorithm ("LD_LBFGS", "LD_SLSQP", "LD_MMA", "LD_TNEWTON" ...; NULL = LD_LBFGS), as
+ * nloptutil::unconstrained::grad_based::bounded::solve sets one up (external/nlopt-util/include/nlopt-util.hpp:226-274): every
+ * callback returns f and the central-difference gradient over the free dofs from one GPU batch. */
+int optimo_perform_optimization_gradient(void* h, int explicit_termination, const char* algorithm, double* final_value, int* evals);
 
 /* Host-only (no GPU): generate + NVRTC-compile the scene-specialised objective kernel of the current scene
  * (include/omo.h: omo_jit_probe). Returns 0 when it compiled; `log` = stack placement summary and compiler log. */

@@ -93,6 +93,7 @@ _CORE_SIG = {
     "optimo_set_stop_optimization": (None, [_vp, ci]),
     "optimo_get_stop_optimization": (ci, [_vp]),
     "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
+    "optimo_perform_optimization_gradient": (ci, [_vp, ci, cs, _dp, _ip]),
     "optimo_probe_specialised_kernel": (ci, [_vp, ci, ci, cs, cs, ci]),
     "optimo_record_solve_trace": (None, [_vp, ci]),
     "optimo_solve_trace_size": (ci, [_vp, _ip, _ip]),
@@ -523,6 +524,12 @@ class Core:
         """Returns (final objective value, function evaluations)."""
         v, n = C.c_double(0.0), C.c_int(0)
         self._ck(_core.optimo_perform_optimization(self.h, int(explicit_termination), C.byref(v), C.byref(n)))
+        return v.value, n.value
+
+    def PerformOptimizationWithGradient(self, explicit_termination=False, algorithm="LD_LBFGS"):
+        """Gradient-based solve (finite-difference gradient on the GPU). Returns (final objective value, function evaluations)."""
+        v, n = C.c_double(0.0), C.c_int(0)
+        self._ck(_core.optimo_perform_optimization_gradient(self.h, int(explicit_termination), algorithm.encode(), C.byref(v), C.byref(n)))
         return v.value, n.value
 
     def probe_specialised_kernel(self, fk=False, count=False, dump_prefix=None):

@@ -182,6 +182,15 @@ int optimo_perform_optimization(void* h, int explicit_termination, double* final
     });
 }
 
+int optimo_perform_optimization_gradient(void* h, int explicit_termination, const char* algorithm, double* final_value, int* evals)
+{
+    return guarded([&] {
+        C(h)->PerformOptimizationWithGradient(explicit_termination != 0, algorithm ? algorithm : "LD_LBFGS");
+        if (final_value) *final_value = C(h)->last_solve_value_;
+        if (evals) *evals = C(h)->last_solve_evals_;
+    });
+}
+
 int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump_prefix, char* log, int cap)
 {
     int status = 0;

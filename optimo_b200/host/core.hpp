@@ -55,6 +55,11 @@ public:
 
     /// core_opt.cpp:60-157 -- LN_BOBYQA over the free dofs through NLopt (loaded at run time, see core_opt.cpp).
     void PerformOptimization(bool explicit_termination = false);
+    /// Next row N1: the same solve driven by a gradient-based NLopt algorithm, as the reference's helper
+    /// nloptutil::unconstrained::grad_based::bounded::solve would set it up (nlopt-util.hpp:226-274) -- every callback
+    /// returns f and the central-difference gradient over the free dofs from one sparse GPU batch (include/omo.h:
+    /// omo_eval_grad). Bounds on t_b / t_f are pulled in by the difference step so that x +- h stays feasible.
+    void PerformOptimizationWithGradient(bool explicit_termination = false, const std::string& algorithm = "LD_LBFGS");
 
     /// core_rbdl.cpp:348-401. Like the reference it leaves the object at `x`.
     double CalculateFullObjective(double min_t, double max_t, const VecN& x, const VecN& x_original);
@@ -107,6 +112,7 @@ public:
     /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
     void InitializeDynamicsModel();
 
+    void Solve(bool explicit_termination, const char* algorithm, bool want_gradient);   // body of both PerformOptimization forms
     /// Result of the last PerformOptimization (function value, evaluations).
     double last_solve_value_ = 0.0;
     int last_solve_evals_ = 0;

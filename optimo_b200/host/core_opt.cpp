@@ -17,6 +17,8 @@ namespace optimo {
 
 namespace {
 
+constexpr double kGradientStep = 1e-4;   // central-difference step of the gradient-based solve
+
 typedef double (*nlopt_func)(unsigned n, const double* x, double* gradient, void* func_data);
 typedef struct nlopt_opt_s* nlopt_opt;
 
@@ -120,7 +122,15 @@ double trampoline(unsigned n, const double* x, double* grad, void* p)
 
 }  // namespace
 
-void Core::PerformOptimization(bool explicit_termination)
+void Core::PerformOptimization(bool explicit_termination) { Solve(explicit_termination, "LN_BOBYQA", false); }
+
+void Core::PerformOptimizationWithGradient(bool explicit_termination, const std::string& algorithm)
+{
+    if (algorithm.size() < 2 || algorithm[1] != 'D') throw std::invalid_argument("PerformOptimizationWithGradient needs a gradient-based (LD_ / GD_) NLopt algorithm");
+    Solve(explicit_termination, algorithm.c_str(), true);
+}
+
+void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gradient)
 {
     stop_optimization_ = false;
     constexpr int dim = 5;
@@ -139,8 +149,9 @@ void Core::PerformOptimization(bool explicit_termination)
     for (int i = 0; i < n; ++i) {
         upper[i * dim + 2] = +M_PI * 0.4;
         lower[i * dim + 2] = -M_PI * 0.4;
-        upper[i * dim + 3] = -epsilon;
-        lower[i * dim + 4] = +epsilon;
+        // a central difference evaluates x +- h e_k: keep the handles on their side of zero there too
+        upper[i * dim + 3] = -(epsilon + (want_gradient ? kGradientStep : 0.0));
+        lower[i * dim + 4] = +(epsilon + (want_gradient ? kGradientStep : 0.0));
     }
     for (size_t i = 0; i < x_initial.size(); ++i) x_initial[i] = std::max(std::min(x_initial[i], upper[i]), lower[i]);
 
@@ -151,6 +162,8 @@ void Core::PerformOptimization(bool explicit_termination)
     data.max_t = max_frame_ + 2.0;
     data.x_original = x_original;
     data.x_initial = x_initial;
+    data.want_gradient = want_gradient;
+    data.gradient_step = kGradientStep;
     for (size_t i = 0; i < freezed_dofs_.size(); ++i) if (!freezed_dofs_[i]) data.free_indices.push_back(static_cast<int>(i));
     const unsigned M = static_cast<unsigned>(data.free_indices.size());
     auto sel = [&](const VecN& v) { VecN r(M); for (unsigned k = 0; k < M; ++k) r[k] = v[data.free_indices[k]]; return r; };
@@ -169,7 +182,9 @@ void Core::PerformOptimization(bool explicit_termination)
 
     // nloptutil::solve (nlopt-util.hpp:44-195)
     NloptApi& api = nlopt_api();
-    nlopt_opt solver = api.create(api.algorithm_from_string("LN_BOBYQA"), M);
+    const int alg = api.algorithm_from_string(algorithm);
+    if (alg < 0) throw std::invalid_argument(std::string("unknown NLopt algorithm ") + algorithm);
+    nlopt_opt solver = api.create(alg, M);
     if (!solver) throw std::runtime_error("nlopt_create failed");
     const VecN u = sel(upper), l = sel(lower);
     api.set_upper_bounds(solver, u.data());
@@ -186,7 +201,7 @@ void Core::PerformOptimization(bool explicit_termination)
     double initial_cost_value = 0.0;
     bool cancelled = false;
     try {
-        std::vector<double> dummy(M);
+        std::vector<double> dummy;   // empty: the banner wants f only, whatever the algorithm
         initial_cost_value = EvaluateObjective(x_star, dummy, &data);
     } catch (const forced_stop&) {
         cancelled = true;

@@ -88,3 +88,43 @@ def test_fox_tail_solve_replay_parity(oracle_port):
     assert np.array_equal(x_after[idx], X[np.argmin(F)])
     frozen = np.setdiff1d(np.arange(x_after.size), idx)
     assert np.array_equal(x_after[frozen], x_init[frozen])
+
+
+@pytest.mark.gpu
+@needs_nlopt
+@pytest.mark.parametrize("algorithm", ["LD_LBFGS", "LD_SLSQP"])
+def test_fox_tail_gradient_based_solve(oracle_port, algorithm):
+    """Next row N1: the fox-tail solve driven by a gradient-based NLopt algorithm; every callback's f and
+    finite-difference gradient come from one sparse GPU batch (omo_eval_grad). The values the solver saw are replayed on the
+    CPU oracle; the descent must at least match what 2000 BOBYQA evaluations reach (f_final of the committed golden)."""
+    from optimo_b200.core import Core
+
+    c = Core(scene_path("fox-tail"))
+    c.select_items(TAIL)
+    x_before = c.GetDescriptor()
+    c.record_solve_trace(True)
+    f_final, evals = c.PerformOptimizationWithGradient(False, algorithm)
+    X, F = c.solve_trace()
+    assert X.shape[1] == 27 and 5 < evals <= 2000
+
+    orc = oracle_port.Oracle(scene_path("fox-tail"), "port")
+    orc.select_items(TAIL)
+    idx = orc.free_indices()
+    x_orig = orc.original()
+    x_init = x_before.copy()
+    worst = 0.0
+    for xf, f in list(zip(X, F))[:: max(1, len(F) // 40)]:
+        full = x_init.copy()
+        full[idx] = xf
+        fo = orc.full_objective(full, x_orig)[0]
+        worst = max(worst, abs(f - fo) / abs(fo))
+    assert worst <= 1e-9, worst
+    with open(SOLVE_GOLDEN) as fh:
+        g = json.load(fh)
+    assert f_final <= F[0] and f_final == F.min()
+    assert f_final < 1.5 * g["f_final"], (f_final, g["f_final"], evals)
+    # handles stayed on their side of zero with room for the difference step
+    x_after = c.GetDescriptor().reshape(-1, 5)
+    assert (x_after[:, 3] < 0).all() and (x_after[:, 4] > 0).all()
+    with pytest.raises(Exception):
+        c.PerformOptimizationWithGradient(False, "LN_BOBYQA")
