@@ -474,9 +474,23 @@ omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
             std::fputs(spec.source.c_str(), fh); std::fclose(fh);
         }
     }
+    // cubins are cached per process by the hash of their source: a second context on the same scene (another Core, another
+    // device) skips NVRTC
+    static std::mutex cache_mutex;
+    static std::map<uint64_t, std::vector<char>> cubin_cache;
+    const uint64_t key = omo_jit::fnv1a(spec.source + "#sub" + std::to_string(spec.sub));
     std::vector<char> cubin;
-    std::string log;
-    if (!omo_jit::compile(spec.source, cubin, log, spec.sub)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+    {
+        std::lock_guard<std::mutex> g(cache_mutex);
+        auto it = cubin_cache.find(key);
+        if (it != cubin_cache.end()) cubin = it->second;
+    }
+    if (cubin.empty()) {
+        std::string log;
+        if (!omo_jit::compile(spec.source, cubin, log, spec.sub)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+        std::lock_guard<std::mutex> g(cache_mutex);
+        cubin_cache[key] = cubin;
+    }
     if (a.cuModuleLoadData(&k.mod, cubin.data()) != 0) { ctx->jit_log = "cuModuleLoadData failed"; return nullptr; }
     size_t bytes = 0;
     if (a.cuModuleGetFunction(&k.fn, k.mod, "omo_jit_kernel") != 0 || a.cuModuleGetGlobal(&k.d_scene, &bytes, k.mod, "c_scene") != 0 ||
