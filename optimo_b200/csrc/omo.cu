@@ -937,7 +937,8 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     const size_t bytes = (size_t)B * ctx->D * sizeof(double);
     // a chunk is at least 4 MB and at least ~8 waves of objective blocks
     const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 4736;
-    const int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(8, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));
+    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));   // 4 measured best on stick240 (1.26 ms; 2: 1.30, 8: 1.33)
+    if (const char* e = std::getenv("OMO_EVAL_CHUNKS")) n_chunks = std::max(1, std::min(8, std::min(B, std::atoi(e))));
     if (n_chunks == 1) {
         OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
         if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
