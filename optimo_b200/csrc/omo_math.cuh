@@ -32,9 +32,18 @@ __constant__ double c_sincos[18] = {
     2.48015872894767294178e-05, -1.38888888888741095749e-03, 4.16666666666666019037e-02,
     1.0e5};
 
+// out of line: the full-range routine is ~90 instructions that no joint angle ever executes -- inlined at each of a walk's
+// sin/cos sites it would be a seventh of the specialised kernel's code
+__device__ __noinline__ double2 sincos_full_range(const double x)
+{
+    double2 r;
+    sincos(x, &r.x, &r.y);
+    return r;   // by value: the callers' sin / cos stay in registers
+}
+
 __device__ __forceinline__ void sincos_angle(const double x, double* __restrict__ s_out, double* __restrict__ c_out)
 {
-    if (!(fabs(x) <= c_sincos[17])) { sincos(x, s_out, c_out); return; }   // also catches NaN / inf
+    if (!(fabs(x) <= c_sincos[17])) { const double2 r = sincos_full_range(x); *s_out = r.x; *c_out = r.y; return; }   // also catches NaN / inf
     // k = nearest integer to x * 2/pi (magic-number rounding), r = x - k*pi/2 in three exact-product steps
     const double t = fma(x, c_sincos[0], c_sincos[1]);
     const int k = __double2loint(t);

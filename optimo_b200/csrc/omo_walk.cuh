@@ -137,6 +137,7 @@ struct Walker {
             // the tile table itself, so the block start is two dependent global round trips deep, not three
             tsg = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
             if (sorted) {
+#pragma unroll 1
                 for (int i = tid; i < S.n_keyed; i += NT) wbase[i] = stage_base(i);
             }
         } else {
