@@ -343,7 +343,24 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def _reserve_stdout():
+    """The contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its version line on fd 1 when the first
+    communicator comes up), so fd 1 is pointed at stderr for the run and the line goes to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(saved, "w")
+
+
 def main():
+    global print
+    out = _reserve_stdout()
+    _print = print
+
+    def print(*a, **k):   # noqa: A001 -- only the result lines use print() in this file
+        k.setdefault("file", out)
+        _print(*a, **k)
+        out.flush()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
