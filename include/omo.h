@@ -132,6 +132,16 @@ omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_ter
 /* Joint world positions p (N_s x 3J, sample-major) of descriptor x (SetStates' p output, core_rbdl.cpp:150-153). */
 omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out);
 
+/* Next row N2/N3: the state of descriptor x at M arbitrary times, as Core::CalculateTorques /
+ * Core::SetCurrentState compute it one t at a time on the UI thread (core_rbdl.cpp:168-198, 264-289): Euler angles at
+ * t - dt, t, t + dt (curves and IK, joint.cpp:36-52), 3-point central differences (core_rbdl.cpp:97-106), one RBDL
+ * InverseDynamics per time. All M times are one launch of the per-sample-output kernel over a grid of (t - dt, t,
+ * t + dt) triples. q, qd, qdd, tau: [M][dof] (q[0:3] = root offset as in SetCurrentState); root_euler: [M][3], the
+ * root joint's own Joint::GetEulerAngle(t) (what Core::ExportMotion writes for it, core_io.cpp:252-294); p: [M][3J]
+ * joint world positions. Any output may be NULL. The objective window set by omo_set_window is left as it was. */
+omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times, int M, double dt, double* q, double* qd,
+                              double* qdd, double* tau, double* root_euler, double* p);
+
 /* NEW (no reference counterpart): central-difference gradient on the free parameters,
  *   g_k = (f(x + h e_idx[k]) - f(x - h e_idx[k])) / (2h),
  * evaluated as ONE batch of 2F+1 columns built on the device from x. f0_out, fpm_out ([F][2] = f+, f-) optional. */

@@ -88,6 +88,19 @@ int optimo_cache_size(void* h, int* n_samples, int* dof); /* Core::GetOptimizati
 int optimo_get_cache(void* h, int which, double* out);    /* 0 time, 1 q, 2 q_dot, 3 q_ddot, 4 tau, 5 local_cost */
 void optimo_clear_optimization_cache(void* h);
 
+/* Next rows N2 / N3. Core::CalculateTorques(t) (core_rbdl.cpp:264-289) of the current object for M times
+ * in one launch: tau [M][dof]; q, qd, qdd optional (SetCurrentState, core_rbdl.cpp:168-198). */
+int optimo_calculate_torques(void* h, const double* times, int M, double* tau, double* q, double* qd, double* qdd);
+int optimo_euler_angles(void* h, const double* times, int M, double* out);   /* Joint::GetEulerAngle of every joint, [M][3J] */
+int optimo_update_maximum_torque_and_cost(void* h, double* max_torque, double* max_cost);   /* core.cpp:105-116 */
+int optimo_export_motion(void* h, const char* path);                  /* Core::ExportMotion, core_io.cpp:252-264 */
+int optimo_motion_json(void* h, char* out, int cap);                  /* the text ExportMotion writes; returns the length */
+int optimo_push_history(void* h);                                     /* core_io.cpp:188-192 */
+int optimo_pop_history(void* h);                                      /* core_io.cpp:194-208 */
+void optimo_clear_history(void* h);
+int optimo_history_size(void* h);
+int optimo_write_history(void* h, const char* path);                  /* core_io.cpp:171-186 */
+
 void* optimo_engine(void* h);                                   /* the omo_ctx* behind this Core (include/omo.h) */
 void* optimo_engine_synced(void* h, double min_t, double max_t); /* same, after pushing window/weights/x_original */
 

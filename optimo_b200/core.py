@@ -89,6 +89,16 @@ _CORE_SIG = {
     "optimo_calculate_gradient": (ci, [_vp, cd, cd, _dp, _dp, ci, _ip, ci, cd, _dp, _dp, _dp]),
     "optimo_positions": (ci, [_vp, cd, cd, _dp, ci, _dp]),
     "optimo_num_samples": (ci, [_vp, cd, cd]),
+    "optimo_calculate_torques": (ci, [_vp, _dp, ci, _dp, _dp, _dp, _dp]),
+    "optimo_euler_angles": (ci, [_vp, _dp, ci, _dp]),
+    "optimo_update_maximum_torque_and_cost": (ci, [_vp, _dp, _dp]),
+    "optimo_export_motion": (ci, [_vp, cs]),
+    "optimo_motion_json": (ci, [_vp, C.c_char_p, ci]),
+    "optimo_push_history": (ci, [_vp]),
+    "optimo_pop_history": (ci, [_vp]),
+    "optimo_clear_history": (None, [_vp]),
+    "optimo_history_size": (ci, [_vp]),
+    "optimo_write_history": (ci, [_vp, cs]),
     "optimo_evaluate_objective": (ci, [_vp, _dp, ci, _dp, ci, cd, cd, ci, cd, _dp, _dp]),
     "optimo_set_stop_optimization": (None, [_vp, ci]),
     "optimo_get_stop_optimization": (ci, [_vp]),
@@ -499,6 +509,58 @@ class Core:
         p = np.zeros((n, 3 * self.J))
         self._ck(_core.optimo_positions(self.h, min_t, max_t, xp, xa.size, p.ctypes.data_as(_dp)))
         return p
+
+    # ---- next rows N2 / N3 ----------------------------------------------------------------------
+    def CalculateTorques(self, t, want_states=False):
+        """Core::CalculateTorques (core_rbdl.cpp:264-289) of the current object. A scalar t gives tau[dof]; a sequence of
+        M times is ONE launch and gives tau[M, dof]. want_states: also (q, qd, qdd) of SetCurrentState (:168-198)."""
+        scalar = np.isscalar(t)
+        ta, tp = _d(np.atleast_1d(t))
+        dof = 3 * self.J
+        outs = [np.zeros((ta.size, dof)) for _ in range(4 if want_states else 1)]
+        ptrs = [o.ctypes.data_as(_dp) for o in outs] + [None] * (4 - len(outs))
+        self._ck(_core.optimo_calculate_torques(self.h, tp, ta.size, *ptrs))
+        if scalar:
+            outs = [o[0] for o in outs]
+        return tuple(outs) if want_states else outs[0]
+
+    def CalculateEulerAngles(self, times):
+        """Joint::GetEulerAngle(t) (joint.cpp:36-52) of every joint, root included: [M, 3J]."""
+        ta, tp = _d(np.atleast_1d(times))
+        e = np.zeros((ta.size, 3 * self.J))
+        self._ck(_core.optimo_euler_angles(self.h, tp, ta.size, e.ctypes.data_as(_dp)))
+        return e
+
+    def UpdateMaximumTorqueAndCost(self):
+        a, b = C.c_double(0.0), C.c_double(0.0)
+        self._ck(_core.optimo_update_maximum_torque_and_cost(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def ExportMotion(self, path):
+        self._ck(_core.optimo_export_motion(self.h, str(path).encode()))
+
+    def motion_json(self):
+        n = _core.optimo_motion_json(self.h, None, 0)
+        if n < 0:
+            self._ck(1)
+        buf = C.create_string_buffer(n + 1)
+        _core.optimo_motion_json(self.h, buf, n + 1)
+        return buf.value.decode()
+
+    def PushHistory(self):
+        self._ck(_core.optimo_push_history(self.h))
+
+    def PopHistory(self):
+        self._ck(_core.optimo_pop_history(self.h))
+
+    def ClearHistory(self):
+        _core.optimo_clear_history(self.h)
+
+    def GetHistorySize(self):
+        return _core.optimo_history_size(self.h)
+
+    def WriteHistory(self, path):
+        self._ck(_core.optimo_write_history(self.h, str(path).encode()))
 
     def EvaluateObjective(self, x_free, x_initial, min_t=None, max_t=None, want_gradient=False, h=1e-4):
         lo, hi = self.window

@@ -635,6 +635,27 @@ omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig)
     return launch_objective(ctx, P, 1, true, true, ctx->d_f, ctx->d_terms);
 }
 
+// Makes `grid` the sample times of every following launch (time-ordered within each warp: the segment search of the
+// table-driven kernel warm-starts from its warp's first sample). Everything sized by N_s / n_tiles is invalidated.
+omo_status install_grid(omo_ctx* ctx, std::vector<double>& grid, double dt)
+{
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->tgrid.swap(grid);
+    ctx->N_s = (int)ctx->tgrid.size();
+    ctx->dt = dt;
+    const int t_max = kBlockThreads - 4;
+    ctx->n_tiles = (ctx->N_s + t_max - 1) / t_max;
+    ctx->T_out = (ctx->N_s + ctx->n_tiles - 1) / ctx->n_tiles;
+    omo_status st = upload(ctx, &ctx->d_tgrid, ctx->tgrid);
+    if (st != OMO_OK) return st;
+    refresh_residues(ctx);
+    ctx->wcost_dirty = true; ctx->p_orig_dirty = true;
+    ctx->sp_valid = false;  // the sparse-gradient item lists are per time grid
+    ctx->cap = 0;  // partial[] depends on n_tiles
+    ctx->out_cap_samples = 0;
+    return OMO_OK;
+}
+
 omo_status ensure_ready(omo_ctx* ctx)
 {
     if (!ctx->have_window) return fail(ctx, OMO_NOT_READY, "omo_set_window has not been called");
@@ -816,21 +837,10 @@ omo_status omo_set_window(omo_ctx* ctx, double min_t, double max_t, double dt)
         if (grid.size() > (size_t)(1 << 24)) return fail(ctx, OMO_BAD_ARG, "time grid too long");
     }
     if (grid.size() < 3) return fail(ctx, OMO_BAD_ARG, "the window must hold at least 3 samples");
-    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->tgrid.swap(grid);
-    ctx->N_s = (int)ctx->tgrid.size();
-    ctx->min_t = min_t; ctx->max_t = max_t; ctx->dt = dt;
-    const int t_max = kBlockThreads - 4;
-    ctx->n_tiles = (ctx->N_s + t_max - 1) / t_max;
-    ctx->T_out = (ctx->N_s + ctx->n_tiles - 1) / ctx->n_tiles;
-    omo_status st = upload(ctx, &ctx->d_tgrid, ctx->tgrid);
+    omo_status st = install_grid(ctx, grid, dt);
     if (st != OMO_OK) return st;
-    refresh_residues(ctx);
+    ctx->min_t = min_t; ctx->max_t = max_t;
     ctx->have_window = true;
-    ctx->wcost_dirty = true; ctx->p_orig_dirty = true;
-    ctx->sp_valid = false;  // the sparse-gradient item lists are per time grid
-    ctx->cap = 0;  // partial[] depends on n_tiles
-    ctx->out_cap_samples = 0;
     return OMO_OK;
 }
 
@@ -1005,6 +1015,84 @@ omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
     OMO_CUDA(cudaMemcpyAsync(p_out, ctx->d_op, (size_t)ctx->N_s * 3 * ctx->J * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
     return OMO_OK;
+}
+
+omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times, int M, double dt, double* q, double* qd,
+                              double* qdd, double* tau, double* root_euler, double* p)
+{
+    if (!ctx || !x || M < 0 || (M > 0 && !times) || !(dt > 0.0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx->have_weights || !ctx->have_original) return fail(ctx, OMO_NOT_READY, "omo_set_weights / omo_set_original have not been called");
+    if (M == 0) return OMO_OK;
+    for (int i = 0; i < M; ++i) if (!std::isfinite(times[i])) return fail(ctx, OMO_BAD_ARG, "non-finite time");
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    // passes of time-ordered, non-overlapping triples (t_k + dt <= t_{k+1} - dt): the frames of a motion are one pass
+    std::vector<int> order(M);
+    for (int i = 0; i < M; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return times[a] < times[b]; });
+    const bool had_window = ctx->have_window;
+    const double w_min = ctx->min_t, w_max = ctx->max_t, w_dt = ctx->dt;
+    const size_t dof = (size_t)3 * ctx->J;
+    constexpr int kMaxTriples = 1 << 18;
+    std::vector<char> done(M, 0);
+    std::vector<int> take;
+    std::vector<double> grid, h[6];
+    int left = M;
+    omo_status st = OMO_OK;
+    double* d_w = nullptr; double* d_root = nullptr;
+    while (left > 0 && st == OMO_OK) {
+        take.clear(); grid.clear();
+        double last_end = -INFINITY;
+        for (int k = 0; k < M && (int)take.size() < kMaxTriples; ++k) {
+            const int i = order[k];
+            if (done[i]) continue;
+            const double t = times[i];
+            if (!(t - dt >= last_end)) continue;
+            grid.push_back(t - dt); grid.push_back(t); grid.push_back(t + dt);   // core_rbdl.cpp:186-188
+            last_end = t + dt;
+            take.push_back(i); done[i] = 1;
+        }
+        left -= (int)take.size();
+        const int n = (int)take.size(), N = 3 * n;
+        ctx->have_window = false;
+        if ((st = install_grid(ctx, grid, dt)) != OMO_OK) break;
+        if ((st = ensure_capacity(ctx, 1)) != OMO_OK) break;
+        if ((st = ensure_outputs(ctx)) != OMO_OK) break;
+        if ((st = dev_alloc(ctx, &d_w, (size_t)N)) != OMO_OK) break;
+        if ((st = dev_alloc(ctx, &d_root, (size_t)N * 3)) != OMO_OK) break;
+        OMO_CUDA(cudaMemsetAsync(d_w, 0, (size_t)N * sizeof(double), ctx->stream));
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        if ((st = activate_scene(ctx)) != OMO_OK) break;
+        if ((st = run_prepare(ctx, ctx->d_X, 1)) != OMO_OK) break;
+        OmoEvalParams P;
+        fill_params(ctx, P);
+        P.wcost = d_w; P.p_orig = nullptr; P.triplet = 1; P.o_root = d_root;
+        P.o_q = ctx->d_oq; P.o_qd = ctx->d_oqd; P.o_qdd = ctx->d_oqdd; P.o_tau = ctx->d_otau; P.o_local = ctx->d_olocal; P.o_p = ctx->d_op;
+        if ((st = launch_objective(ctx, P, 1, true, true, ctx->d_f, ctx->d_terms)) != OMO_OK) break;
+        // only the middle sample of each triple is read back (strided copies, row = one sample)
+        double* outs[6] = {q, qd, qdd, tau, p, root_euler};
+        const double* srcs[6] = {ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_op, d_root};
+        for (int a = 0; a < 6; ++a) {
+            if (!outs[a]) continue;
+            const size_t w = (a == 5 ? 3 : dof) * sizeof(double);
+            h[a].resize((size_t)n * (a == 5 ? 3 : dof));
+            OMO_CUDA(cudaMemcpy2DAsync(h[a].data(), w, srcs[a] + (a == 5 ? 3 : dof), 3 * w, w, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+        }
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int a = 0; a < 6; ++a) {
+            if (!outs[a]) continue;
+            const size_t w = (a == 5 ? 3 : dof);
+            for (int k = 0; k < n; ++k) std::memcpy(outs[a] + (size_t)take[k] * w, h[a].data() + (size_t)k * w, w * sizeof(double));
+        }
+    }
+    if (d_w) cudaFree(d_w);
+    if (d_root) cudaFree(d_root);
+    // put the objective window back (p_original and the cost weights are rebuilt on the next evaluation)
+    ctx->have_window = false;
+    if (had_window) {
+        const omo_status st2 = omo_set_window(ctx, w_min, w_max, w_dt);
+        if (st == OMO_OK) st = st2;
+    }
+    return st;
 }
 
 omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin, int col_count,

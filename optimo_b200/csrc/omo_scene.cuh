@@ -111,6 +111,12 @@ struct OmoEvalParams {
     // optional per-sample outputs of candidate 0 (OptimizationCache, core.h:120-152); sample-major
     double *o_q, *o_qd, *o_qdd, *o_tau, *o_local, *o_p;
     unsigned long long* counters;  // [4] or null
+    // OUT instance only (next row N2, Core::CalculateTorques / SetCurrentState, core_rbdl.cpp:168-198,264-289):
+    // triplet != 0: the grid is a list of (t - dt, t, t + dt) triples and every sample takes the 3-point central forms
+    // (core_rbdl.cpp:97-106); only the middle sample of each triple is meaningful. o_root: [N_s][3] Euler angles of the
+    // root joint's own rot channels (Joint::GetEulerAngle of the root, joint.cpp:36-52; q[0:3] holds its offset instead).
+    int triplet;
+    double* o_root;
 };
 
 #endif

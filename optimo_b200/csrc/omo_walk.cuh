@@ -166,7 +166,7 @@ struct Walker {
         const int s_raw = tile * P.T_out - 2 + idx;
         s = min(max(s_raw, 0), N - 1);
         owned = (idx >= 2) && (s_raw < tile_end) && (s_raw >= 0) && item_valid;
-        interior = (s >= 2) && (s <= N - 3);
+        interior = (s >= 2) && (s <= N - 3) && !(OUT && P.triplet != 0);
         t = __ldg(P.tgrid + s);
         tsq = (!OUT && interior) ? S.static_tsq : 0.0;   // the pruned bodies' share (candidate-independent)
         dtr = 0.0;
@@ -188,6 +188,7 @@ struct Walker {
 #pragma unroll
             for (int k = 0; k < 3; ++k)
                 e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], t, sorted, n_bez, n_newton) : S.chan_const[k];
+            if (OUT && owned && P.o_root) { P.o_root[s * 3] = e[0]; P.o_root[s * 3 + 1] = e[1]; P.o_root[s * 3 + 2] = e[2]; }
             double sx, cx, sy, cy, sz, cz;
             sincos_angle(e[0], &sx, &cx); sincos_angle(e[1], &sy, &cy); sincos_angle(e[2], &sz, &cz);
             L[0] = cz * cy; L[1] = cz * sy * sx - sz * cx; L[2] = cz * sy * cx + sz * sx;

@@ -242,6 +242,38 @@ int optimo_get_cache(void* h, int which, double* out)
 }
 void optimo_clear_optimization_cache(void* h) { C(h)->ClearOptimizationCache(); }
 
+// ---- next rows N2 / N3 --------------------------------------------------------------------------------------------------
+int optimo_calculate_torques(void* h, const double* times, int M, double* tau, double* q, double* qd, double* qdd)
+{
+    return guarded([&] { C(h)->CalculateTorquesBatch(times, M, tau, q, qd, qdd); });
+}
+int optimo_euler_angles(void* h, const double* times, int M, double* out)
+{
+    return guarded([&] { const auto v = C(h)->CalculateEulerAngles(times, M); std::copy(v.begin(), v.end(), out); });
+}
+int optimo_update_maximum_torque_and_cost(void* h, double* max_torque, double* max_cost)
+{
+    return guarded([&] {
+        C(h)->UpdateMaximumTorqueAndCost();
+        if (max_torque) *max_torque = C(h)->max_torque_;
+        if (max_cost) *max_cost = C(h)->max_cost_;
+    });
+}
+int optimo_export_motion(void* h, const char* path) { return guarded([&] { C(h)->ExportMotion(path); }); }
+int optimo_motion_json(void* h, char* out, int cap)
+{
+    std::string s;
+    const int rc = guarded([&] { s = C(h)->ConvertMotionToJson(); });
+    if (rc) return -1;
+    if (out && cap > 0) { std::strncpy(out, s.c_str(), cap - 1); out[cap - 1] = 0; }
+    return static_cast<int>(s.size());
+}
+int optimo_push_history(void* h) { return guarded([&] { C(h)->PushHistory(); }); }
+int optimo_pop_history(void* h) { return guarded([&] { C(h)->PopHistory(); }); }
+void optimo_clear_history(void* h) { C(h)->ClearHistory(); }
+int optimo_history_size(void* h) { return C(h)->GetHistorySize(); }
+int optimo_write_history(void* h, const char* path) { return guarded([&] { C(h)->WriteHistory(path); }); }
+
 void* optimo_engine(void* h)
 {
     void* e = nullptr;

@@ -153,7 +153,7 @@ void Core::ReadJson(const std::string& file_path)
 /// core_io.cpp:228-250 (ApplyJsonToScene) + :154-163 (rebuild the dynamics model). The runtime state that the
 /// reference keeps only in UI-driven members (frozen dofs, weights, kernels, x_original) is
 /// reset to the Core() defaults for the new scene.
-void Core::ReadJsonString(const std::string& json_text)
+void Core::ApplyJsonToScene(const std::string& json_text)
 {
     const Json json = Json::parse(json_text);
     object_->SetRootJoint(nullptr);
@@ -165,7 +165,11 @@ void Core::ReadJsonString(const std::string& json_text)
     object_->SetRootJoint(InterpretJson2Joint(json["joints"]));
     for (const Json& h : json["ik_handlers"].array_items()) InterpretJson2IkHandlerAndAddToObject(h, object_);
     ClearOptimizationCache();
+}
 
+void Core::ReadJsonString(const std::string& json_text)
+{
+    ApplyJsonToScene(json_text);
     const int n = static_cast<int>(object_->GetDescriptor().size()) / 5;
     freezed_dofs_.assign(static_cast<size_t>(n) * 5, false);
     for (int i = 0; i < n; ++i) { freezed_dofs_[i * 5 + 0] = true; freezed_dofs_[i * 5 + 1] = true; }
@@ -202,6 +206,88 @@ void Core::WriteJson(const std::string& file_path) const
 {
     std::ofstream out(file_path);
     out << ConvertCurrentSceneToJson();
+}
+
+// ---- history / motion export (next row N3) ------------------------------------------------------------------------
+
+void Core::WriteHistory(const std::string& file_path) const
+{
+    std::ofstream out(file_path);
+    out << "[";
+    bool first = true;
+    for (const std::string& stamp : history_) {
+        if (!first) out << ",";
+        first = false;
+        out << stamp;
+    }
+    out << "]";
+}
+
+void Core::PushHistory() { history_.push_back(ConvertCurrentSceneToJson()); }
+
+void Core::PopHistory()
+{
+    if (history_.size() <= 1) return;   // "Cannot undo any more." (core_io.cpp:198-202)
+    history_.pop_back();
+    ApplyJsonToScene(history_.back());
+    // The reference leaves model_ as it is (an undo never changes the skeleton in its UI); here the engine snapshots the
+    // scene, so it is rebuilt whenever the stamp differs structurally -- InitializeDynamicsModel just drops it.
+    const size_t n = object_->GetDescriptor().size();
+    if (x_original_.size() != n) {
+        x_original_ = object_->GetDescriptor();
+        freezed_dofs_.assign(n, false);
+        for (size_t i = 0; i < n / 5; ++i) { freezed_dofs_[i * 5] = true; freezed_dofs_[i * 5 + 1] = true; }
+        per_item_weights_.assign(object_->GetItems().size(), 0.0);
+    }
+    InitializeDynamicsModel();
+}
+
+std::string Core::FrameJson(int frame, const double* euler) const
+{
+    Json joints = Json::array();
+    int i = 0;
+    for (const auto& joint : object_->GetJoints()) {
+        Json j = Json::object();
+        j.set("name", Json::string(joint->name_));
+        j.set("r_x", Json::number(euler[3 * i + 0]));
+        j.set("r_y", Json::number(euler[3 * i + 1]));
+        j.set("r_z", Json::number(euler[3 * i + 2]));
+        joints.push_back(j);
+        ++i;
+    }
+    Json f = Json::object();
+    f.set("frame", Json::number(frame));
+    f.set("joints", joints);
+    return f.dump();
+}
+
+std::string Core::ConvertSpecificFrameToJson(int t)
+{
+    const double tt = t;
+    const std::vector<double> e = CalculateEulerAngles(&tt, 1);
+    return FrameJson(t, e.data());
+}
+
+std::string Core::ConvertMotionToJson()
+{
+    // every frame's angles in ONE launch (the reference evaluates curve by curve, frame by frame: core_io.cpp:256-262)
+    std::vector<double> times;
+    for (int t = min_frame_; t <= max_frame_; ++t) times.push_back(t);
+    const std::vector<double> e = CalculateEulerAngles(times.data(), static_cast<int>(times.size()));
+    const size_t w = 3 * object_->GetJoints().size();
+    std::string out = "[";
+    for (int t = min_frame_; t <= max_frame_; ++t) {
+        if (t != min_frame_) out += ", ";
+        out += FrameJson(t, e.data() + (size_t)(t - min_frame_) * w);
+    }
+    out += "]";
+    return out;
+}
+
+void Core::ExportMotion(const std::string& file_path)
+{
+    std::ofstream out(file_path);
+    out << ConvertMotionToJson();
 }
 
 // ---- weights / frozen dofs ------------------------------------------------------------------------------------------
@@ -336,10 +422,15 @@ int Core::ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_pr
 /// Called at the top of every evaluation so that mid-solve slider changes behave as in the reference.
 void Core::SyncEngine(double min_t, double max_t, const VecN& x_original)
 {
+    Check(omo_set_window(Engine(), min_t, max_t, 0.20), "omo_set_window");   // dt = 0.20, core_rbdl.cpp:351
+    SyncEngineState(x_original);
+}
+
+void Core::SyncEngineState(const VecN& x_original)
+{
     omo_ctx* e = Engine();
     const VecN w = CalculateParameterWeights();
     if (x_original.size() != w.size()) throw std::invalid_argument("x_original has the wrong length");
-    Check(omo_set_window(e, min_t, max_t, 0.20), "omo_set_window");   // dt = 0.20, core_rbdl.cpp:351
     std::vector<omo_gauss> ks;
     for (const GaussianKernel& k : kernels_) ks.push_back(omo_gauss{k.amp, k.mu, k.sigma});
     Check(omo_set_weights(e, w.data(), static_cast<int>(w.size()), weight_trajectory_, ks.data(), static_cast<int>(ks.size()),
@@ -388,6 +479,46 @@ std::vector<double> Core::CalculatePositions(double min_t, double max_t, const V
     std::vector<double> p(static_cast<size_t>(omo_num_samples(engine_)) * omo_dof(engine_));
     Check(omo_positions(engine_, x.data(), p.data()), "omo_positions");
     return p;
+}
+
+// ---- next row N2: single-t torques (core_rbdl.cpp:264-289) and their UI-side consumers -----------------------------
+
+void Core::CalculateTorquesBatch(const double* times, int M, double* tau, double* q, double* qd, double* qdd)
+{
+    const VecN x = object_->GetDescriptor();
+    SyncEngineState(x_original_.size() == x.size() ? x_original_ : x);
+    Check(omo_eval_states_at(engine_, x.data(), times, M, 0.20, q, qd, qdd, tau, nullptr, nullptr), "omo_eval_states_at");
+}
+
+VecN Core::CalculateTorques(double t)
+{
+    VecN tau(3 * object_->GetJoints().size(), 0.0);
+    CalculateTorquesBatch(&t, 1, tau.data());
+    return tau;
+}
+
+std::vector<double> Core::CalculateEulerAngles(const double* times, int M)
+{
+    const VecN x = object_->GetDescriptor();
+    SyncEngineState(x_original_.size() == x.size() ? x_original_ : x);
+    const size_t dof = 3 * object_->GetJoints().size();
+    std::vector<double> e(static_cast<size_t>(M) * dof), root(static_cast<size_t>(M) * 3);
+    Check(omo_eval_states_at(engine_, x.data(), times, M, 0.20, e.data(), nullptr, nullptr, nullptr, root.data(), nullptr), "omo_eval_states_at");
+    // q[0:3] is the root OFFSET (core_rbdl.cpp:178-182); ExportMotion wants the root joint's own angles there
+    for (int i = 0; i < M; ++i) for (int k = 0; k < 3; ++k) e[i * dof + k] = root[3 * static_cast<size_t>(i) + k];
+    return e;
+}
+
+void Core::UpdateMaximumTorqueAndCost()
+{
+    const OptimizationCache cache = GetOptimizationCache();
+    max_torque_ = 0.0; max_cost_ = 0.0;
+    for (int i = 0; i < cache.GetSize(); ++i) {
+        double n2 = 0.0;
+        for (double v : cache.tau[i]) n2 += v * v;
+        max_torque_ = std::max(max_torque_, std::sqrt(n2));
+        max_cost_ = std::max(max_cost_, cache.local_cost_sequence[i]);
+    }
 }
 
 Core::OptimizationCache Core::GetOptimizationCache()

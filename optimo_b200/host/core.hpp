@@ -77,6 +77,26 @@ public:
     void WriteJson(const std::string& file_path) const;   // core_io.cpp:165-169
     std::string ConvertCurrentSceneToJson() const;        // core_io.cpp:216-226
 
+    // ---- next rows N2 / N3: the callers either side of the path ------------------------------------
+    /// core_rbdl.cpp:264-289: joint torques of the CURRENT object at time t (3-point differences over t -+ 0.2,
+    /// SetCurrentState core_rbdl.cpp:168-198). One GPU launch; see CalculateTorquesBatch for many t at once.
+    VecN CalculateTorques(double t);
+    /// The same for M times in one launch (the UI's heat strip asks for one t per pixel column, graphwidget.cpp:325-340).
+    /// tau [M][dof] row-major; q / qd / qdd optional, same shape.
+    void CalculateTorquesBatch(const double* times, int M, double* tau, double* q = nullptr, double* qd = nullptr, double* qdd = nullptr);
+    /// Joint::GetEulerAngle(t) of every joint in GetJoints() order, root included (joint.cpp:36-52), M x 3J, on the GPU.
+    std::vector<double> CalculateEulerAngles(const double* times, int M);
+    double max_torque_ = 0.0, max_cost_ = 0.0;            // core.h:96-97
+    void UpdateMaximumTorqueAndCost();                    // core.cpp:105-116
+    void WriteHistory(const std::string& file_path) const;          // core_io.cpp:171-186
+    void PushHistory();                                            // core_io.cpp:188-192
+    void PopHistory();                                             // core_io.cpp:194-208 (undo: re-applies the previous stamp)
+    void ClearHistory() { history_.clear(); }                      // core_io.cpp:210-213
+    int GetHistorySize() const { return static_cast<int>(history_.size()); }
+    void ExportMotion(const std::string& file_path);                // core_io.cpp:252-264
+    std::string ConvertSpecificFrameToJson(int t);                  // core_io.cpp:266-294
+    std::string ConvertMotionToJson();                              // the text ExportMotion writes
+
     struct OptimizationCache {  // core.h:120-131
         std::vector<double> time_sequence;
         std::vector<VecN> q, q_dot, q_ddot, tau;
@@ -125,6 +145,10 @@ public:
 
 private:
     void SyncEngine(double min_t, double max_t, const VecN& x_original);
+    void SyncEngineState(const VecN& x_original);   // weights + x_original, no window
+    void ApplyJsonToScene(const std::string& json_text);   // core_io.cpp:228-250
+    std::string FrameJson(int frame, const double* euler) const;
+    std::vector<std::string> history_;              // core.h: std::list<std::string> history_
     void Check(omo_status st, const char* what);
 
     std::vector<GaussianKernel> kernels_;

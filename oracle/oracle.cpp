@@ -670,6 +670,38 @@ struct Scene {
         return C + D_param + D_traj;
     }
 
+    // ---- N2: Core::SetCurrentState + Core::CalculateTorques   core_rbdl.cpp:168-198, 264-289 -------------------
+    // Scalar differences of core_rbdl.cpp:97-106: (succ - prev) / (2 eps), (succ - 2 v + prev) / (eps eps).
+    void SetCurrentState(double t, double dt, VecN* q, VecN* qd, VecN* qdd)
+    {
+        int i = 0;
+        for (Joint* j : GetJoints()) {
+            if (!j->parent) {
+                for (int k = 0; k < 3; ++k) (*q)[k] = j->offset[k];
+            } else {
+                const V3 e = j->GetEulerAngle(t), ep = j->GetEulerAngle(t - dt), es = j->GetEulerAngle(t + dt);
+                for (int k = 0; k < 3; ++k) {
+                    (*q)[i * 3 + k] = e[k];
+                    (*qd)[i * 3 + k] = (es[k] - ep[k]) / (2.0 * dt);
+                    (*qdd)[i * 3 + k] = (es[k] - 2.0 * e[k] + ep[k]) / (dt * dt);
+                }
+            }
+            ++i;
+        }
+    }
+    VecN CalculateTorques(double t, VecN* q_out = nullptr, VecN* qd_out = nullptr, VecN* qdd_out = nullptr)
+    {
+        const double dt = 0.20;
+        const int dof = static_cast<int>(model->dof_count());
+        VecN q(dof, 0.0), qd(dof, 0.0), qdd(dof, 0.0), tau(dof, 0.0);
+        SetCurrentState(t, dt, &q, &qd, &qdd);
+        model->inverse_dynamics(q, qd, qdd, tau);
+        if (q_out) *q_out = q;
+        if (qd_out) *qd_out = qd;
+        if (qdd_out) *qdd_out = qdd;
+        return tau;
+    }
+
     // ---- a2: select / revert   core_opt.cpp:99-121 ---------------------------------------------------
     std::vector<int> FreeIndices() const
     {
@@ -865,6 +897,35 @@ int orc_positions(void* h, double min_t, double max_t, const double* x, int n, d
     s->SetStates(min_t, max_t, 0.20, static_cast<int>(s->model->dof_count()), &ts, &q, &qd, &qdd, &p);
     for (const VecN& r : p) { std::copy(r.begin(), r.end(), p_out); p_out += r.size(); }
     return static_cast<int>(ts.size());
+}
+
+/// N2: Core::CalculateTorques(t) (core_rbdl.cpp:264-289) of descriptor x at M times; tau / q / qd / qdd are [M][dof] (any NULL).
+void orc_torques_at(void* h, const double* x, int n, const double* times, int M, double* tau, double* q, double* qd, double* qdd)
+{
+    Scene* s = static_cast<Scene*>(h);
+    s->SetDescriptor(VecN(x, x + n));
+    const size_t dof = s->model->dof_count();
+    for (int i = 0; i < M; ++i) {
+        VecN a, b, c;
+        const VecN T = s->CalculateTorques(times[i], &a, &b, &c);
+        if (tau) std::copy(T.begin(), T.end(), tau + i * dof);
+        if (q) std::copy(a.begin(), a.end(), q + i * dof);
+        if (qd) std::copy(b.begin(), b.end(), qd + i * dof);
+        if (qdd) std::copy(c.begin(), c.end(), qdd + i * dof);
+    }
+}
+
+/// N3: what Core::ConvertSpecificFrameToJson reads (core_io.cpp:264-294): Joint::GetEulerAngle(t) of EVERY joint in
+/// GetJoints() order, the root's own rot channels included. out is [M][3J].
+void orc_euler_angles_at(void* h, const double* x, int n, const double* times, int M, double* out)
+{
+    Scene* s = static_cast<Scene*>(h);
+    s->SetDescriptor(VecN(x, x + n));
+    for (int i = 0; i < M; ++i)
+        for (Joint* j : s->GetJoints()) {
+            const V3 e = j->GetEulerAngle(times[i]);
+            for (int k = 0; k < 3; ++k) *out++ = e[k];
+        }
 }
 
 /// a1/a2: EvaluateObjective (core_opt.cpp:42-57) with revert(x) = X^T x + Y x_initial.

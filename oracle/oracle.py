@@ -79,6 +79,8 @@ def _load(kind):
         "orc_dof": (ci, [vp]),
         "orc_get_cache": (None, [vp, ci, _dp]),
         "orc_positions": (ci, [vp, cd, cd, _dp, ci, _dp]),
+        "orc_torques_at": (None, [vp, _dp, ci, _dp, ci, _dp, _dp, _dp, _dp]),
+        "orc_euler_angles_at": (None, [vp, _dp, ci, _dp, ci, _dp]),
         "orc_evaluate_objective": (cd, [vp, _dp, ci, _dp, ci, cd, cd]),
         "orc_gradient": (cd, [vp, _dp, ci, cd, cd, cd, _dp, _dp]),
         "orc_probe_inverse_dynamics": (None, [ci, _ip, _ip, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp, _dp]),
@@ -245,6 +247,22 @@ class Oracle:
         p = np.zeros((n, 3 * self.J))
         self.lib.orc_positions(self.h, lo, hi, xp, xa.size, p.ctypes.data_as(_dp))
         return p
+
+    def torques_at(self, x, times):
+        """Core::CalculateTorques(t) (core_rbdl.cpp:264-289) for every t: dict of tau, q, qd, qdd, each [M, dof]."""
+        xa, xp = _d(x)
+        ta, tp = _d(times)
+        out = {k: np.zeros((ta.size, self.dof)) for k in ("tau", "q", "qd", "qdd")}
+        self.lib.orc_torques_at(self.h, xp, xa.size, tp, ta.size, *[out[k].ctypes.data_as(_dp) for k in ("tau", "q", "qd", "qdd")])
+        return out
+
+    def euler_angles_at(self, x, times):
+        """Joint::GetEulerAngle(t) of every joint (root included), [M, 3J] -- what Core::ExportMotion writes."""
+        xa, xp = _d(x)
+        ta, tp = _d(times)
+        e = np.zeros((ta.size, 3 * self.J))
+        self.lib.orc_euler_angles_at(self.h, xp, xa.size, tp, ta.size, e.ctypes.data_as(_dp))
+        return e
 
     def gradient(self, x, h=1e-4, window=None):
         """Central-difference gradient on the free parameters. Returns (f0, grad[F], fpm[F,2])."""

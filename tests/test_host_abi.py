@@ -141,3 +141,27 @@ def test_compute_fails_loudly_without_a_gpu():
     x = c.GetDescriptor()
     with pytest.raises(EngineError, match="no usable CUDA device"):
         c.CalculateFullObjective(-1.0, 42.0, x, x)
+
+
+def test_history_stack_and_files_need_no_gpu(tmp_path):
+    """Next row N3: PushHistory / PopHistory / WriteHistory (core_io.cpp:171-213) are host-side text handling."""
+    c = Core(scene_path("conductor"))
+    x = c.GetDescriptor()
+    c.PushHistory()
+    s0 = c.scene_json()
+    x2 = x.copy()
+    x2[2::5] -= 0.05
+    c.SetDescriptor(x2)
+    c.PushHistory()
+    h = tmp_path / "history.json"
+    c.WriteHistory(h)
+    assert h.read_text() == "[" + s0 + "," + c.scene_json() + "]"
+    assert len(json.loads(h.read_text())) == 2
+    c.PopHistory()
+    assert c.GetHistorySize() == 1 and c.scene_json() == s0 and np.array_equal(c.GetDescriptor(), x)
+    c.PopHistory()
+    assert c.GetHistorySize() == 1
+    c.ClearHistory()
+    assert c.GetHistorySize() == 0
+    with pytest.raises(EngineError):
+        c.CalculateTorques(3.0)       # the torque query itself is GPU work: no fallback
