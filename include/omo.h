@@ -180,6 +180,12 @@ void* omo_stream(omo_ctx* ctx); /* cudaStream_t the hot path launches on */
 omo_status omo_set_counting(omo_ctx* ctx, int enable);
 omo_status omo_get_counters(omo_ctx* ctx, unsigned long long* out5);
 
+/* Single-candidate calls (omo_eval with B = 1 -- what the NLopt callback EvaluateObjective, OptiMo/core_opt.cpp:42-57, makes
+ * thousands of times per solve): the copy-in / prepare / objective / finish / copy-out chain is captured once as a CUDA
+ * graph and replayed with one launch for as long as window, buffers and launch geometry stay what they were (weights,
+ * x_original and kernels may change between calls). OMO_GRAPH=0 switches it off. Returns the number of replays so far. */
+unsigned long long omo_graph_replays(const omo_ctx* ctx);
+
 /* Timing of the main objective kernel: accumulates CUDA-event time of every launch between reset and read. */
 omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* launches);
 

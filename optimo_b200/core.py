@@ -149,6 +149,7 @@ _OMO_SIG = {
     "omo_jit_info": (ci, [_vp, C.POINTER(_ull), cs, ci]),
     "omo_selftest_division": (ci, [_vp, _dp, _dp, ci, _dp, _dp, _ip]),
     "omo_grad_sparsity": (ci, [_vp, C.POINTER(_ull)]),
+    "omo_graph_replays": (_ull, [_vp]),
 }
 for _n, (_r, _a) in _OMO_SIG.items():
     _sig(_omo, _n, _r, _a)
@@ -297,6 +298,10 @@ class Engine:
         out = (_ull * 5)()
         self._ck(_omo.omo_get_counters(self.h, out), "omo_get_counters")
         return {"bezier_evals": out[0], "newton_iters": out[1], "ik_solves": out[2], "ik_iters": out[3], "launches": out[4]}
+
+    def graph_replays(self):
+        """Single-candidate evaluations served by replaying the captured CUDA graph (include/omo.h)."""
+        return int(_omo.omo_graph_replays(self.h))
 
     def kernel_timing(self, reset=0):
         ms, n = C.c_double(0.0), C.c_int(0)

@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""Latency of ONE objective evaluation through the callback API (Core::CalculateFullObjective -> omo_eval, B = 1), the call
+NLopt makes per iteration (BASELINE.json configs[1]): CUDA-graph replay (default) against plain launches (OMO_GRAPH=0), and
+the wall time of the reference's BOBYQA set-up on fox-tail with either. Run on the GPU box:  python profiles/latency_single.py"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def per_call(scene, graph, n=3000):
+    os.environ["OMO_GRAPH"] = "1" if graph else "0"
+    from optimo_b200.core import Core
+    c = Core(os.path.join(ROOT, "tests", "golden", "scenes", scene + ".json"))
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    rng = np.random.default_rng(0)
+    X = x0 + 1e-3 * rng.standard_normal((16, x0.size)) * (np.arange(x0.size) % 5 == 2)
+    for i in range(50):
+        c.CalculateFullObjective(lo, hi, X[i % 16], x0)
+    t0 = time.perf_counter()
+    for i in range(n):
+        c.CalculateFullObjective(lo, hi, X[i % 16], x0)
+    us = (time.perf_counter() - t0) / n * 1e6
+    return us, c.engine().graph_replays()
+
+
+def solve(graph):
+    os.environ["OMO_GRAPH"] = "1" if graph else "0"
+    from optimo_b200.core import Core
+    c = Core(os.path.join(ROOT, "tests", "golden", "scenes", "fox-tail.json"))
+    c.select_items(["tail_root", "tail_center"])
+    c.CalculateFullObjective(*c.window, c.GetDescriptor(), c.GetDescriptor())
+    t0 = time.perf_counter()
+    f, evals = c.PerformOptimization(False)
+    return (time.perf_counter() - t0) * 1e3, evals, f
+
+
+if __name__ == "__main__":
+    out = {}
+    for scene in ("fox-tail", "stick-figure", "conductor"):
+        a, _ = per_call(scene, False)
+        b, r = per_call(scene, True)
+        out[scene] = {"plain_us_per_call": round(a, 2), "graph_us_per_call": round(b, 2), "graph_replays": r}
+    try:
+        ms0, ev0, f0 = solve(False)
+        ms1, ev1, f1 = solve(True)
+        out["fox-tail BOBYQA solve"] = {"plain_ms": round(ms0, 1), "graph_ms": round(ms1, 1), "evals": [ev0, ev1], "f": [f0, f1]}
+    except Exception as e:   # NLopt missing on the box
+        out["fox-tail BOBYQA solve"] = {"error": str(e)}
+    print(json.dumps(out, indent=1))

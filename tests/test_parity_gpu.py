@@ -332,3 +332,37 @@ def test_sparse_gradient_columns_equal_dense_evaluation(monkeypatch, name):
     assert 0 < executed
     if name == "stick240":
         assert executed < dense_items / 3      # 10 tiles per column, one or two of them within reach of a control point
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_single_candidate_graph_replay_equals_plain_launches(monkeypatch, name):
+    """omo_eval with B = 1 (the NLopt callback's call, core_opt.cpp:42-57) replays a captured CUDA graph from its third
+    call on. Same kernels, same order: bit-identical to the plain launch sequence (OMO_GRAPH=0), across weight, kernel,
+    x_original and window changes made between calls (what the dialogs do mid-solve, sliderdialog.cpp:71-76)."""
+    def run(graph):
+        monkeypatch.setenv("OMO_GRAPH", "1" if graph else "0")
+        c = Core(scene_path(name))
+        x0 = c.GetDescriptor()
+        idx = c.free_indices()
+        lo, hi = c.window
+        out = []
+        r = np.random.default_rng(11)
+        for step in range(12):
+            x = x0.copy()
+            x[idx] += 0.01 * r.standard_normal(idx.size)
+            if step == 4:
+                c.UpdateGlobalWeight(12.5)                 # w_traj: 0 -> 12.5 switches the FK instance of the kernel
+            if step == 7:
+                c.set_kernels([(1.0, 0.5 * (lo + hi), 2.0)])
+            if step == 9:
+                hi = hi - 3.0                              # another window: other grid, other buffers
+            f, terms = c.CalculateFullObjective(lo, hi, x, x0 if step < 10 else x, want_terms=True)
+            out.append((f,) + tuple(terms))
+        return np.array(out), c.engine().graph_replays(), c.engine().counters()["launches"]
+
+    plain, n_plain, l_plain = run(False)
+    graph, n_graph, l_graph = run(True)
+    assert n_plain == 0
+    assert n_graph >= 4, n_graph
+    assert l_graph == l_plain           # replays are counted as the kernels they launch
+    assert np.array_equal(plain, graph)
