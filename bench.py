@@ -7,6 +7,7 @@ A "step" is one pass of the hot path over one batch of synthetic candidates:
   workload stick240 (default; BASELINE.json configs[3], the one `north_star`'s target is quoted on):
       4096 candidate edits of the stick-figure skeleton x 240 frames  -> 4096 x 1216 = 4.98 M sample-evals / GPU / step
   workload grad : the 937-column finite-difference batch of one objective+gradient evaluation of that scene
+  workload grad_stick / grad_conductor: the same for the shipped stick-figure / conductor scenes (configs[0] / configs[2])
   workload tree64: BASELINE.json configs[4], 64-joint tree x 2000 frames, 256 candidates
 N > 1 (torchrun, one process per GPU): every rank evaluates its own candidates (weak scaling, no data-path collective);
 the per-candidate scalars are all-gathered over NCCL inside the timed step.
@@ -48,6 +49,13 @@ def make_workload(name, rank=0):
         scene = synthetic.tree_scene(64, 2000)
         B = 256
         desc = "64-joint tree x 2000 frames, 256 candidates (BASELINE.json configs[4])"
+    elif name in ("grad_stick", "grad_conductor"):
+        # BASELINE.json configs[0] / configs[2]: one objective + finite-difference gradient of a shipped scene
+        with open(os.path.join(ROOT, "tests", "golden", "scenes", {"grad_stick": "stick-figure", "grad_conductor": "conductor"}[name] + ".json")) as fh:
+            scene = json.load(fh)
+        B = 1
+        desc = {"grad_stick": "resources/scene-stick-figure.json (BASELINE.json configs[0])",
+                "grad_conductor": "resources/scene-conductor.json, IK handle + 2 Gaussian kernels + w_traj 12.5 (BASELINE.json configs[2])"}[name]
     else:
         raise SystemExit(f"unknown workload {name}")
     return scene, B, desc
@@ -152,21 +160,26 @@ def run_ours(args):
 
     scene, B, desc = make_workload(args.workload, rank)
     core = Core(scene, device=local)
+    if args.workload == "grad_conductor":
+        core.set_kernels([(1.0, 20.0, 2.6), (1.0, 10.0, 1.0)])
+        core.UpdateGlobalWeight(12.5)
     x0 = core.GetDescriptor()
     lo, hi = core.window
     eng = core.engine(synced_window=(lo, hi))
     N_s, D, J = eng.num_samples, eng.D, core.J
     idx = core.free_indices()
 
-    if args.workload == "grad":
+    grad = args.workload.startswith("grad")
+    if grad:
         B = 2 * idx.size + 1
         x_base = synthetic.perturbed_candidates(x0, 1, first=0)[0]
         X = np.tile(x_base, (B, 1))
         for k, i in enumerate(idx):
             X[2 * k + 1, i] += 1e-4
             X[2 * k + 2, i] -= 1e-4
-        desc = (f"one objective+gradient evaluation = {B} finite-difference columns of the stick-figure x 240 frames scene, "
-                "through omo_eval_grad_columns (columns evaluated only on the tiles their control point reaches; value = executed sample-evals/s)")
+        desc = (f"one objective+gradient evaluation = {B} finite-difference columns of "
+                + ("the stick-figure x 240 frames scene" if args.workload == "grad" else desc) +
+                ", through omo_eval_grad_columns (columns evaluated only on the tiles their control point reaches; value = executed sample-evals/s)")
     else:
         X = synthetic.perturbed_candidates(x0, B, first=rank * B)
 
@@ -179,8 +192,6 @@ def run_ours(args):
     Xp[:] = X
     Fp = eng.pinned_array((B,))
     eng.h2d(dX.data_ptr(), X)
-
-    grad = args.workload == "grad"
 
     def step_device():
         if grad:   # the finite-difference columns through the API: built on the device, sparse over tiles (include/omo.h)
@@ -309,7 +320,7 @@ def run_ours(args):
     from oracle import oracle as O
     cores = os.cpu_count() or 1
     sample = max(cores, min(B, 64 * cores))
-    if args.workload == "grad" or world > 1 or args.no_cpu_baseline:
+    if grad or world > 1 or args.no_cpu_baseline:
         cpu = None
     else:
         leg = cpu_reference_leg(scene, sample, 0, x0)
@@ -330,12 +341,12 @@ def run_ours(args):
         "config": {"workload": desc, "candidates_per_gpu": B, "samples_per_candidate": N_s, "joints": J, "descriptor": D,
                    "l2": "flushed between timed iterations (256 MiB memset)", "gather": "nccl all_gather of f" if world > 1 else "none"},
         "clocks": sampler.summary() if sampler else None,
-        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int((D + 4 * idx.size) if grad else B * D * 8), "d2h_bytes_per_step": int(B * 8)},
+        "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int((8 * D + 4 * idx.size) if grad else B * D * 8), "d2h_bytes_per_step": int(B * 8)},
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu,
         "executed_fraction_of_dense_sample_evals": executed_frac,
         "objective_evals_per_s": B * world / (ms_dev * 1e-3), "frame_evals_per_s": value / 5.0,
-        "objective_plus_gradient_evals_per_s": (world / (ms_dev * 1e-3)) if args.workload == "grad" else (B * world / (2 * idx.size + 1)) / (ms_dev * 1e-3),
+        "objective_plus_gradient_evals_per_s": (world / (ms_dev * 1e-3)) if grad else (B * world / (2 * idx.size + 1)) / (ms_dev * 1e-3),
         "wall_s": {"device_loop": wall_dev, "e2e_loop": wall_e2e},
     }
     print(json.dumps(line), flush=True)
@@ -366,7 +377,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="stick240", choices=["stick240", "tree64", "grad"])
+    ap.add_argument("--workload", default="stick240", choices=["stick240", "tree64", "grad", "grad_stick", "grad_conductor"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="development runs: skip the timed CPU leg (cpu_baseline = null)")
     args = ap.parse_args()
     if args.impl == "reference":
