@@ -28,30 +28,43 @@ def per_call(scene, graph, n=3000):
     for i in range(n):
         c.CalculateFullObjective(lo, hi, X[i % 16], x0)
     us = (time.perf_counter() - t0) / n * 1e6
-    return us, c.engine().graph_replays()
+    for i in range(20):
+        c.CalculateGradient(lo, hi, X[i % 16], x0)       # first call compiles the scene-specialised kernel (NVRTC)
+    t0 = time.perf_counter()
+    for i in range(n // 10):
+        c.CalculateGradient(lo, hi, X[i % 16], x0)
+    us_g = (time.perf_counter() - t0) / (n // 10) * 1e6
+    return us, c.engine().graph_replays(), us_g, c.engine().jit_info()["compile_ms"]
 
 
-def solve(graph):
+def solve(graph, algorithm=None):
     os.environ["OMO_GRAPH"] = "1" if graph else "0"
     from optimo_b200.core import Core
     c = Core(os.path.join(ROOT, "tests", "golden", "scenes", "fox-tail.json"))
     c.select_items(["tail_root", "tail_center"])
-    c.CalculateFullObjective(*c.window, c.GetDescriptor(), c.GetDescriptor())
+    x = c.GetDescriptor()
+    c.CalculateFullObjective(*c.window, x, x)
+    if algorithm:
+        c.CalculateGradient(*c.window, x, x)     # NVRTC outside the timed solve
     t0 = time.perf_counter()
-    f, evals = c.PerformOptimization(False)
+    f, evals = c.PerformOptimizationWithGradient(False, algorithm) if algorithm else c.PerformOptimization(False)
     return (time.perf_counter() - t0) * 1e3, evals, f
 
 
 if __name__ == "__main__":
     out = {}
     for scene in ("fox-tail", "stick-figure", "conductor"):
-        a, _ = per_call(scene, False)
-        b, r = per_call(scene, True)
-        out[scene] = {"plain_us_per_call": round(a, 2), "graph_us_per_call": round(b, 2), "graph_replays": r}
+        a = per_call(scene, False)
+        b = per_call(scene, True)
+        out[scene] = {"plain_us_per_call": round(a[0], 2), "graph_us_per_call": round(b[0], 2), "graph_replays": b[1],
+                      "objective_plus_gradient_us_per_call": round(b[2], 2), "nvrtc_compile_ms": b[3]}
     try:
         ms0, ev0, f0 = solve(False)
         ms1, ev1, f1 = solve(True)
         out["fox-tail BOBYQA solve"] = {"plain_ms": round(ms0, 1), "graph_ms": round(ms1, 1), "evals": [ev0, ev1], "f": [f0, f1]}
+        for alg in ("LD_SLSQP", "LD_LBFGS"):
+            ms, ev, f = solve(True, alg)
+            out[f"fox-tail {alg} solve"] = {"ms": round(ms, 1), "callbacks": ev, "f": f}
     except Exception as e:   # NLopt missing on the box
         out["fox-tail BOBYQA solve"] = {"error": str(e)}
     print(json.dumps(out, indent=1))
