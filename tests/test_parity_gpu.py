@@ -366,3 +366,35 @@ def test_single_candidate_graph_replay_equals_plain_launches(monkeypatch, name):
     assert n_graph >= 4, n_graph
     assert l_graph == l_plain           # replays are counted as the kernels they launch
     assert np.array_equal(plain, graph)
+
+
+@pytest.mark.parametrize("root,nb", [("LeftForeArm", 1), ("LeftArm", 2), ("LeftShoulder", 3), ("Spine", 4)])
+def test_ik_chain_lengths_match_oracle(monkeypatch, oracle_port, root, nb):
+    """IkHandler chains of 1-4 bodies (ikhandler.cpp:166-188: one EulerZYX body per joint between root and end effector):
+    the IK solve is specialised on the chain length for 1, 2 and 3 bodies and generic beyond (ik_solve_n, omo_kernels.cuh).
+    The conductor scene with its handle's root moved up and down the left arm, table-driven and scene-specialised kernel."""
+    import copy
+    scene = copy.deepcopy(load_scene("conductor"))
+    scene["ik_handlers"][0]["root_name"] = root
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1); o.set_weight_trajectory(12.5)
+    rng = np.random.default_rng(nb)
+    res = {}
+    for mode in ("0", "1"):
+        _forced(monkeypatch, mode)
+        c = Core(scene)
+        c.UpdateGlobalWeight(12.5)
+        x0 = c.GetDescriptor()
+        X = np.stack([x0, x0])
+        X[1, 2::5] += 0.1 * (np.random.default_rng(nb).random(x0.size // 5) - 0.5)
+        lo, hi = c.window
+        c.engine(synced_window=(lo, hi)).set_counting(True)
+        res[mode] = c.CalculateFullObjectiveBatch(lo, hi, X, x0)
+        k = c.engine().counters()
+        assert k["ik_solves"] == 2 * c.engine().num_samples, k
+        assert k["ik_iters"] >= k["ik_solves"]
+        if mode == "1":
+            assert c.engine().jit_info()["launches"] > 0, c.engine().jit_info()["log"]
+    assert np.allclose(res["1"], res["0"], rtol=1e-13, atol=0), (res["1"], res["0"])
+    for b in range(2):
+        fo, _ = o.full_objective(X[b], x0)
+        assert abs(res["0"][b] - fo) <= TOL * abs(fo), (root, b, res["0"][b], fo)
