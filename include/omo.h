@@ -45,7 +45,10 @@ typedef enum omo_status {
 
 typedef struct omo_ctx omo_ctx;
 
-/* Limits of the sm_100a kernels (scene tables live in constant memory). */
+/* Limits of the sm_100a kernels (scene tables live in constant memory). Any tree shape within OMO_MAX_JOINTS is served:
+ * the walk parks one stack slot per open ancestor and per open branching; what does not fit a block's 227 KB of shared
+ * memory (a binary tree of depth 7 with positions, a chain of more than ~17 joints) goes to per-thread slots. A tree that
+ * needs more than shared memory + 128 per-thread slots (only degenerate "caterpillar" shapes do) is refused with OMO_BAD_ARG. */
 #define OMO_MAX_JOINTS 128
 #define OMO_MAX_IK 8
 #define OMO_MAX_IK_CHAIN 8 /* rotating joints per IK chain (end effector excluded) */

@@ -416,12 +416,12 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
     return OMO_OK;
 }
 
-struct LaunchPlan { int ns, n_tiles, t_out; size_t smem; };
+struct LaunchPlan { int ns, n_tiles, t_out; size_t smem; int smem_slots; bool deep; };
 
-size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns, bool out)
+size_t smem_bytes(const omo_ctx* ctx, bool fk, int ns, bool out, int slots_override = -1)
 {
     const int tree = out ? 0 : 1;
-    const int slots = fk ? ctx->n_slots_fk[tree] : ctx->n_slots_nofk[tree];
+    const int slots = slots_override >= 0 ? slots_override : (fk ? ctx->n_slots_fk[tree] : ctx->n_slots_nofk[tree]);
     const int ex_rows = ctx->hs.n_ex_rows + (ctx->n_ik > 0 ? 6 : 0);
     const size_t seg = (((size_t)(kBlockThreads / 32) * ctx->hs.n_keyed * sizeof(unsigned short)) + 15) & ~(size_t)15;
     return std::max((size_t)(ex_rows + slots * OMO_SLOT) * ns * kBlockThreads * sizeof(double) + seg, (size_t)64 * sizeof(double));
@@ -436,20 +436,32 @@ LaunchPlan make_plan(const omo_ctx* ctx, int B, bool fk, bool ik, bool out)
     p.n_tiles = (ctx->N_s + t_max - 1) / t_max;
     p.t_out = (ctx->N_s + p.n_tiles - 1) / p.n_tiles;
     p.smem = smem_bytes(ctx, fk, p.ns, out);
+    p.deep = false;
+    p.smem_slots = fk ? ctx->n_slots_fk[out ? 0 : 1] : ctx->n_slots_nofk[out ? 0 : 1];
+    if (p.smem > (size_t)227 * 1024) {
+        // deep tree: as many slots as fit stay in shared memory, the rest go per thread (objective_kernel<..., DEEP>, which
+        // always carries the FK steps: one set of deep instances instead of two)
+        const int all = ctx->n_slots_fk[out ? 0 : 1];
+        int fit = all;
+        while (fit > 0 && smem_bytes(ctx, true, p.ns, out, fit) > (size_t)227 * 1024) --fit;
+        p.deep = true; p.smem_slots = fit;
+        p.smem = smem_bytes(ctx, true, p.ns, out, fit);
+        if (all - fit > OMO_DEEP_SLOTS) p.smem = (size_t)1 << 30;   // refused by the launch below
+    }
     return p;
 }
 
-template <bool FK, bool IK, bool OUT, bool COUNT>
+template <bool FK, bool IK, bool OUT, bool COUNT, bool DEEP = false>
 omo_status launch_objective_t(omo_ctx* ctx, const OmoEvalParams& P, int B, const LaunchPlan& plan)
 {
-    if (plan.smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree too deep for the shared-memory stack");
-    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<FK, IK, OUT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
+    if (plan.smem > 227 * 1024) return fail(ctx, OMO_BAD_ARG, "joint tree needs more stack slots than shared memory plus OMO_DEEP_SLOTS per-thread slots hold");
+    OMO_CUDA(cudaFuncSetAttribute(omo::objective_kernel<FK, IK, OUT, COUNT, DEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->timing && !OUT) {
         OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
         OMO_CUDA(cudaEventRecord(e0, ctx->stream));
     }
-    omo::objective_kernel<FK, IK, OUT, COUNT><<<P.n_items, kBlockThreads, plan.smem, ctx->stream>>>(P);
+    omo::objective_kernel<FK, IK, OUT, COUNT, DEEP><<<P.n_items, kBlockThreads, plan.smem, ctx->stream>>>(P);
     OMO_CUDA(cudaGetLastError());
     if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1;
@@ -553,7 +565,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     if (ik || out) fk = true;
     const bool count = P.counters != nullptr && !out;
     const LaunchPlan plan = make_plan(ctx, B, fk, ik, out);
-    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.smem_stride = 0;
+    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.smem_stride = 0; P.n_smem_slots = plan.smem_slots;
     P.item_map = d_item_map;
     P.n_items = d_item_map ? n_items : B * plan.n_tiles;
     omo_status st;
@@ -571,7 +583,12 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
         }
         if (mode == 1) return fail(ctx, OMO_CUDA_ERROR, "OMO_JIT=1 but the specialised kernel is unavailable: " + ctx->jit_log);
     }
-    if (out) st = ik ? launch_objective_t<true, true, true, false>(ctx, P, B, plan) : launch_objective_t<true, false, true, false>(ctx, P, B, plan);
+    if (plan.deep) {
+        if (count) return fail(ctx, OMO_BAD_ARG, "work counters are not available for trees that need the deep-stack kernel");
+        if (out) st = ik ? launch_objective_t<true, true, true, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, true, false, true>(ctx, P, B, plan);
+        else st = ik ? launch_objective_t<true, true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false, true>(ctx, P, B, plan);
+    }
+    else if (out) st = ik ? launch_objective_t<true, true, true, false>(ctx, P, B, plan) : launch_objective_t<true, false, true, false>(ctx, P, B, plan);
     else if (ik) st = count ? launch_objective_t<true, true, false, true>(ctx, P, B, plan) : launch_objective_t<true, true, false, false>(ctx, P, B, plan);
     else if (fk) st = count ? launch_objective_t<true, false, false, true>(ctx, P, B, plan) : launch_objective_t<true, false, false, false>(ctx, P, B, plan);
     else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
@@ -963,7 +980,7 @@ omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_ou
 
 omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_terms* terms_out)
 {
-    if (!ctx || !X || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx || (!X && ctx->D > 0) || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");   // D = 0: a scene without keyed curves
     if (B == 0) return OMO_OK;
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
@@ -1055,7 +1072,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
 omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd, double* qdd,
                            double* tau, double* local_cost)
 {
-    if (!ctx || !x) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx || (!x && ctx->D > 0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
@@ -1075,7 +1092,7 @@ omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_ter
 
 omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
 {
-    if (!ctx || !x || !p_out) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx || (!x && ctx->D > 0) || !p_out) return fail(ctx, OMO_BAD_ARG, "bad argument");
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
@@ -1089,7 +1106,7 @@ omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
 omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times, int M, double dt, double* q, double* qd,
                               double* qdd, double* tau, double* root_euler, double* p)
 {
-    if (!ctx || !x || M < 0 || (M > 0 && !times) || !(dt > 0.0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx || (!x && ctx->D > 0) || M < 0 || (M > 0 && !times) || !(dt > 0.0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
     if (!ctx->have_weights || !ctx->have_original) return fail(ctx, OMO_NOT_READY, "omo_set_weights / omo_set_original have not been called");
     if (M == 0) return OMO_OK;
     for (int i = 0; i < M; ++i) if (!std::isfinite(times[i])) return fail(ctx, OMO_BAD_ARG, "non-finite time");
@@ -1167,7 +1184,7 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
 omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin, int col_count,
                                  double* d_f_cols, int sync)
 {
-    if (!ctx || !x || (F > 0 && !free_idx) || F < 0 || !d_f_cols) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (!ctx || (!x && ctx->D > 0) || (F > 0 && !free_idx) || F < 0 || !d_f_cols) return fail(ctx, OMO_BAD_ARG, "bad argument");
     if (col_begin < 0 || col_count < 0 || col_begin + col_count > 2 * F + 1) return fail(ctx, OMO_BAD_ARG, "column range outside [0, 2F+1)");
     for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
     if (col_count == 0) return OMO_OK;

@@ -10,15 +10,15 @@ namespace omo {
 
 __device__ __forceinline__ int meta_byte(const int w, const int sh) { const int v = (w >> sh) & 0xff; return v == 0xff ? -1 : v; }
 
-template <bool FK, bool IK, bool OUT, bool COUNT>
-__global__ void __launch_bounds__(OMO_NT, 4) objective_kernel(const OmoEvalParams P)
+template <bool FK, bool IK, bool OUT, bool COUNT, bool DEEP = false>
+__global__ void __launch_bounds__(OMO_NT, DEEP ? 1 : 4) objective_kernel(const OmoEvalParams P)
 {
     extern __shared__ double smem[];
     const OmoDevScene& S = c_scene;
-    typedef Walker<FK, IK, OUT, COUNT> W;
+    typedef Walker<FK, IK, OUT, COUNT, DEEP ? OMO_DEEP_SLOTS : 0, 0, false, DEEP> W;
     constexpr int TREE = W::TREE;
     W w(P);
-    w.begin(smem, FK ? S.n_slots_tree[TREE] : S.n_slots_nofk_tree[TREE]);
+    w.begin(smem, DEEP ? P.n_smem_slots : (FK ? S.n_slots_tree[TREE] : S.n_slots_nofk_tree[TREE]));
 
     const int n_act = S.n_act[TREE];
     int bp = 0;                               // the body visited last (starts at the root)

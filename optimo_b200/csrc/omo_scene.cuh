@@ -24,6 +24,7 @@
 #ifndef OMO_SUB
 #define OMO_SUB 1
 #endif
+#define OMO_DEEP_SLOTS 128  // per-thread (local-memory) stack slots of the deep-tree instance of the table-driven kernel
 #define OMO_SLOT 12  // doubles per stack slot: (f, sincos) or (v, a) or (L, t)
 // Prepared Bezier segments (prepare_kernel -> objective kernels): one record of OMO_SEGD doubles per chain position
 // `pos` that closes a segment (pos-1 -> pos of the same channel):
@@ -116,6 +117,7 @@ struct OmoEvalParams {
     // (core_rbdl.cpp:97-106); only the middle sample of each triple is meaningful. o_root: [N_s][3] Euler angles of the
     // root joint's own rot channels (Joint::GetEulerAngle of the root, joint.cpp:36-52; q[0:3] holds its offset instead).
     int triplet;
+    int n_smem_slots;  // deep-tree instance of the table-driven kernel: stack slots held in shared memory, the rest per thread
     double* o_root;
 };
 

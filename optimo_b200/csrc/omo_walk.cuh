@@ -33,7 +33,10 @@ namespace omo {
 // (stage_issue / stage_wait / curve_staged); SEGG = channels per curve group = records rows of one staging buffer.
 // CPT (scene-specialised kernels only): compact stack. A slot argument is then the slot's first ROW of the shared-memory
 // stack (slots are as wide as what is parked in them, 6 to 12 rows), or 4096 + r for per-thread slot r.
-template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0, bool CPT = false>
+// DEEP (table-driven kernel only): trees whose stack does not fit shared memory (a 128-joint chain parks 127 bodies). Slots
+// below `nsm` live in shared memory as usual, slot nsm + r is the per-thread rs[r] (run-time indexed = local memory, which
+// the driver provisions per RESIDENT thread -- the pooling a global scratch buffer would have to re-invent).
+template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0, bool CPT = false, bool DEEP = false>
 struct Walker {
     static constexpr int NT = OMO_NT;
     static constexpr int TREE = OUT ? 0 : 1;   // 0: every body, 1: candidate-independent subtrees pruned
@@ -51,6 +54,7 @@ struct Walker {
     bool sorted;
     unsigned n_bez, n_newton, n_iksolve, n_ikiter;
     int xbuf;
+    int nsm;                    // DEEP: number of stack slots in shared memory
 
     // state of the body visited last (v, a: also the parent state for the next one)
     SV6 v, a, f;
@@ -75,12 +79,14 @@ struct Walker {
     // stack element c of slot sl
     __device__ __forceinline__ double ld(const int sl, const int c) const
     {
-        if (NREG > 0 && sl >= (CPT ? 4096 : 256)) return rs[sl - (CPT ? 4096 : 256)][c];
+        if (DEEP) { if (sl >= nsm) return rs[sl - nsm][c]; }
+        else if (NREG > 0 && sl >= (CPT ? 4096 : 256)) return rs[sl - (CPT ? 4096 : 256)][c];
         return stk[(size_t)((CPT ? sl : sl * OMO_SLOT) + c) * NT];
     }
     __device__ __forceinline__ void st(const int sl, const int c, const double x)
     {
-        if (NREG > 0 && sl >= (CPT ? 4096 : 256)) rs[sl - (CPT ? 4096 : 256)][c] = x;
+        if (DEEP && sl >= nsm) rs[sl - nsm][c] = x;
+        else if (!DEEP && NREG > 0 && sl >= (CPT ? 4096 : 256)) rs[sl - (CPT ? 4096 : 256)][c] = x;
         else stk[(size_t)((CPT ? sl : sl * OMO_SLOT) + c) * NT] = x;
     }
 
@@ -110,6 +116,7 @@ struct Walker {
             tid = threadIdx.x; item = blockIdx.x; item_valid = true;
         }
         sm0 = smem;
+        nsm = n_smem_slots;
         if (P.item_map) item = __ldg(P.item_map + item);   // sparse launches (finite-difference columns): listed (candidate, tile) pairs only
         const int cand = item / P.n_tiles;
         const int tile = item - cand * P.n_tiles;

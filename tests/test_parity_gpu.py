@@ -398,3 +398,54 @@ def test_ik_chain_lengths_match_oracle(monkeypatch, oracle_port, root, nb):
     for b in range(2):
         fo, _ = o.full_objective(X[b], x0)
         assert abs(res["0"][b] - fo) <= TOL * abs(fo), (root, b, res["0"][b], fo)
+
+
+def _rechain(scene):
+    """The joints of a tree_scene re-linked as ONE chain (the deepest tree a joint count allows)."""
+    nodes = list(synthetic.iter_joints(scene["joints"]))
+    for n in nodes:
+        n["children"] = []
+    for a, b in zip(nodes, nodes[1:]):
+        a["children"] = [b]
+    return scene
+
+
+@pytest.mark.parametrize("shape", ["binary", "chain"])
+def test_maximum_joint_count_and_empty_inputs(oracle_port, shape):
+    """Edge sizes of the C ABI (include/omo.h): OMO_MAX_JOINTS = 128 joints as a binary tree (widest sibling stack) and as a
+    single chain (deepest recursion, 127 nested bodies), against the oracle; one joint more is refused, not truncated;
+    an empty batch is a no-op; a scene without any keyed curve (D = 0) evaluates to its constant-motion cost."""
+    scene = synthetic.tree_scene(n_joints=128, n_frames=12, key_every=4)
+    if shape == "chain":
+        scene = _rechain(scene)
+    o = oracle_port.Oracle(scene, "port"); o.set_sampling_concurrency(1); o.set_weight_trajectory(3.0)
+    c = Core(scene)
+    c.UpdateGlobalWeight(3.0)
+    x0 = c.GetDescriptor()
+    X = synthetic.perturbed_candidates(x0, 3)
+    lo, hi = c.window
+    f = c.CalculateFullObjectiveBatch(lo, hi, X, x0)
+    for b in range(3):
+        fo, _ = o.full_objective(X[b], x0)
+        assert abs(f[b] - fo) <= TOL * abs(fo), (shape, b, f[b], fo)
+    assert c.CalculateFullObjectiveBatch(lo, hi, X[:0], x0).size == 0
+
+    too_many = synthetic.tree_scene(n_joints=129, n_frames=12, key_every=4)
+    if shape == "chain":
+        too_many = _rechain(too_many)
+    with pytest.raises(EngineError, match="OMO_MAX_JOINTS"):
+        big = Core(too_many)
+        big.CalculateFullObjective(*big.window, big.GetDescriptor(), big.GetDescriptor())
+
+    if shape == "binary":
+        still = synthetic.tree_scene(n_joints=6, n_frames=12, key_every=4)
+        for n in synthetic.iter_joints(still["joints"]):
+            for k, v in (("rot_x", 0.3), ("rot_y", -0.2), ("rot_z", 0.1)):
+                n[k] = {"var": v, "curve": []}
+        cs = Core(still)
+        xs = cs.GetDescriptor()
+        assert xs.size == 0
+        os_ = oracle_port.Oracle(still, "port")
+        fs = cs.CalculateFullObjective(*cs.window, xs, xs)
+        fo, _ = os_.full_objective(xs, xs)
+        assert abs(fs - fo) <= 1e-9 * abs(fo) + 1e-18, (fs, fo)
