@@ -1047,17 +1047,28 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
         // d_X may still be read by kernels queued earlier on `stream`
         OMO_CUDA(cudaEventRecord(ctx->done_ev, ctx->stream));
         OMO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->done_ev, 0));
-        const int per = (B + n_chunks - 1) / n_chunks;
+        // Chunk sizes 1 : 2 : 2 : ... -- the kernels cannot start before the first chunk has landed, so it is half a chunk; the
+        // rest are equal because on this box the copy (~25 GB/s) takes about as long as the evaluation, and the step then ends
+        // one chunk's evaluation after the last copy. OMO_EVAL_CHUNKS_SHAPE=equal | ramp (default) | double (1 : 2 : 4 : ...).
+        int bound[9];
+        const char* shape = std::getenv("OMO_EVAL_CHUNKS_SHAPE");
+        const int mode_c = !shape ? 1 : (std::strcmp(shape, "equal") == 0 ? 0 : (std::strcmp(shape, "double") == 0 ? 2 : 1));
+        for (int c = 0; c <= n_chunks; ++c) {
+            long long num = c, den = n_chunks;
+            if (mode_c == 1) { num = c == 0 ? 0 : 2 * c - 1; den = 2 * n_chunks - 1; }
+            if (mode_c == 2) { num = (1LL << c) - 1; den = (1LL << n_chunks) - 1; }
+            bound[c] = (int)((long long)B * num / den);
+        }
         for (int c = 0; c < n_chunks; ++c) {
-            const int b0 = c * per, nb = std::min(per, B - b0);
-            if (nb <= 0) break;
+            const int b0 = bound[c], nb = bound[c + 1] - b0;
+            if (nb <= 0) continue;
             OMO_CUDA(cudaMemcpyAsync(ctx->d_X + (size_t)b0 * ctx->D, X + (size_t)b0 * ctx->D, (size_t)nb * ctx->D * sizeof(double),
                                      cudaMemcpyHostToDevice, ctx->copy_stream));
             OMO_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
         }
         for (int c = 0; c < n_chunks; ++c) {
-            const int b0 = c * per, nb = std::min(per, B - b0);
-            if (nb <= 0) break;
+            const int b0 = bound[c], nb = bound[c + 1] - b0;
+            if (nb <= 0) continue;
             OMO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0));
             if ((st = eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, ctx->d_f + b0, terms_out ? ctx->d_terms + (size_t)3 * b0 : nullptr)) != OMO_OK)
                 return st;
