@@ -118,6 +118,7 @@ struct omo_ctx {
     std::vector<unsigned long long> sg_key, sg_pending;
     unsigned long long sg_kernels = 0, sg_replays = 0;
     double* h_single = nullptr;                 // pinned: x [D], then f, C, D_param, D_traj
+    double* d_single = nullptr;                 // device: f, C, D_param, D_traj of the single candidate (one copy-out)
 
     // counters / timing
     unsigned long long* d_counters = nullptr;
@@ -623,7 +624,8 @@ omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
     Q.N_s = ctx->N_s; Q.T_out = ctx->T_out; Q.n_tiles = ctx->n_tiles; Q.n_keyed = ctx->hs.n_keyed;
     Q.chunk = std::min(kPrepChunk, std::max(ctx->n_cp, 1));
     const size_t sh = (size_t)6 * (Q.chunk + 1) * sizeof(double);
-    OMO_CUDA(cudaMemsetAsync(ctx->d_flags, 1, (size_t)B * sizeof(unsigned), ctx->stream));   // bit 0 of every word: "sorted"
+    // bit 0 of every flag word = "sorted": preset here when several blocks share a candidate, written by the one block otherwise
+    if (prep_parts(ctx) > 1) OMO_CUDA(cudaMemsetAsync(ctx->d_flags, 1, (size_t)B * sizeof(unsigned), ctx->stream));
     omo::prepare_kernel<<<dim3((unsigned)B, (unsigned)prep_parts(ctx)), 128, sh, ctx->stream>>>(Q);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
@@ -788,7 +790,7 @@ std::vector<unsigned long long> single_key(const omo_ctx* ctx)
     auto bits = [](double v) { unsigned long long u; std::memcpy(&u, &v, sizeof(u)); return u; };
     const void* ptrs[] = {ctx->d_X, ctx->d_prep, ctx->d_dparam, ctx->d_partial, ctx->d_f, ctx->d_terms, ctx->d_flags, ctx->d_seg, ctx->d_tile_seg, ctx->d_tgrid,
                           ctx->d_wcost, ctx->d_wparam, ctx->d_x0, ctx->d_p_orig, ctx->d_cp_of_pos, ctx->d_first_of_pos, ctx->d_last_of_pos, ctx->d_next_same,
-                          ctx->h_single, ctx->d_counters};
+                          ctx->h_single, ctx->d_single, ctx->d_counters};
     std::vector<unsigned long long> k;
     for (const void* p : ptrs) k.push_back((unsigned long long)reinterpret_cast<uintptr_t>(p));
     const long long ints[] = {ctx->N_s, ctx->n_tiles, ctx->T_out, ctx->n_cp, ctx->D, ctx->cyclic, ctx->counting ? 1 : 0, ctx->jit_mode, ctx->n_ik, ctx->cap};
@@ -859,6 +861,7 @@ void omo_destroy(omo_ctx* ctx)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (ctx->sg_exec) cudaGraphExecDestroy(ctx->sg_exec);
     if (ctx->h_single) cudaFreeHost(ctx->h_single);
+    if (ctx->d_single) cudaFree(ctx->d_single);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     for (auto& e : ctx->chunk_ev) if (e) cudaEventDestroy(e);
@@ -997,6 +1000,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
         // The solver's callback: one candidate per call, thousands of calls. The first call with a given state runs the plain
         // path below (it finishes every lazy allocation / module load), the second captures, the rest replay.
         if (!ctx->h_single) OMO_CUDA(cudaHostAlloc((void**)&ctx->h_single, (size_t)(ctx->D + 4) * sizeof(double), cudaHostAllocDefault));
+        if (!ctx->d_single) OMO_CUDA(cudaMalloc((void**)&ctx->d_single, 4 * sizeof(double)));
         jit_mode(ctx);
         const std::vector<unsigned long long> key = single_key(ctx);
         bool replay = ctx->sg_exec != nullptr && key == ctx->sg_key;
@@ -1006,9 +1010,8 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
             cudaGraph_t graph = nullptr;
             OMO_CUDA(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
             cudaError_t ce = cudaMemcpyAsync(ctx->d_X, ctx->h_single, bytes, cudaMemcpyHostToDevice, ctx->stream);
-            st = ce == cudaSuccess ? eval_device_impl(ctx, ctx->d_X, 1, ctx->d_f, ctx->d_terms) : OMO_CUDA_ERROR;
-            if (st == OMO_OK && ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->h_single + ctx->D, ctx->d_f, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-            if (st == OMO_OK && ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->h_single + ctx->D + 1, ctx->d_terms, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+            st = ce == cudaSuccess ? eval_device_impl(ctx, ctx->d_X, 1, ctx->d_single, ctx->d_single + 1) : OMO_CUDA_ERROR;
+            if (st == OMO_OK && ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->h_single + ctx->D, ctx->d_single, 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
             const cudaError_t ee = cudaStreamEndCapture(ctx->stream, &graph);   // always ends the capture, whatever happened inside
             ctx->sg_kernels = ctx->launches - l0;
             ctx->launches = l0;
