@@ -109,7 +109,14 @@ def cpu_reference_leg(scene, B_sample, threads, x0, first=0):
     cores = O.hardware_concurrency(kind) if threads == 0 else threads
     sec, f = o.bench_batch(X, 1, cores)
     n_s = O.time_grid(*o.window, kind=kind).size
-    return {"kind": "reference" if kind == "ref" else "port", "cores": cores, "seconds": sec, "candidates": B_sample, "n_s": int(n_s), "f": f, "X": X}
+    # BASELINE.md section 3, figure i ("ref-as-is"): what OptiMo does today -- candidates one after another, parallel_for over the
+    # time samples for the curve / FK sampling (core_rbdl.cpp:158), serial RNEA loop (core_rbdl.cpp:338). Small sample: it is slow.
+    n_as_is = max(2, min(B_sample, 16))
+    sec0, f0 = o.bench_batch(X[:n_as_is], 0, cores)
+    assert np.array_equal(f0, f[:n_as_is]) or np.allclose(f0, f[:n_as_is], rtol=1e-12, atol=0)
+    return {"kind": "reference" if kind == "ref" else "port", "cores": cores, "seconds": sec, "candidates": B_sample, "n_s": int(n_s), "f": f, "X": X,
+            "as_is": {"value": n_as_is * int(n_s) / sec0, "unit": UNIT, "objective_evals_per_s": n_as_is / sec0,
+                      "sample": f"{n_as_is} candidates one after another, parallel_for over samples on {cores} threads, serial RNEA (the reference's own schedule)"}}
 
 
 def run_reference(args):
@@ -135,7 +142,8 @@ def run_reference(args):
         "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc, "candidates_per_step": sample, "samples_per_candidate": leg["n_s"]},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": leg["cores"], "kind": leg["kind"],
-                         "sample": f"{sample} of {B} candidates per step, candidate-parallel over {leg['cores']} host threads"},
+                         "sample": f"{sample} of {B} candidates per step, candidate-parallel over {leg['cores']} host threads",
+                         "as_is": leg["as_is"]},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "objective_evals_per_s": sample / sec, "frame_evals_per_s": value / 5.0,
     }
@@ -330,7 +338,7 @@ def run_ours(args):
         assert rel <= 1e-9, f"GPU batch deviates from the CPU oracle: {rel}"
         cpu = {"value": cpu_val, "unit": UNIT, "cores": leg["cores"], "kind": leg["kind"],
                "sample": f"first {sample} of {B} candidates, candidate-parallel over {leg['cores']} host threads, {leg['seconds']:.2f} s",
-               "max_rel_diff_vs_gpu": float(rel)}
+               "max_rel_diff_vs_gpu": float(rel), "as_is": leg["as_is"]}
 
     n_total = n_se * executed_frac * world
     value = n_total / (ms_dev * 1e-3)
