@@ -52,6 +52,9 @@ def solve(graph, algorithm=None):
 
 
 if __name__ == "__main__":
+    sys.stdout.flush()
+    result_fd = os.dup(1)      # nlopt-util prints its own summary on fd 1: keep that out of the JSON
+    os.dup2(2, 1)
     out = {}
     for scene in ("fox-tail", "stick-figure", "conductor"):
         a = per_call(scene, False)
@@ -67,4 +70,4 @@ if __name__ == "__main__":
             out[f"fox-tail {alg} solve"] = {"ms": round(ms, 1), "callbacks": ev, "f": f}
     except Exception as e:   # NLopt missing on the box
         out["fox-tail BOBYQA solve"] = {"error": str(e)}
-    print(json.dumps(out, indent=1))
+    os.write(result_fd, (json.dumps(out, indent=1) + "\n").encode())
