@@ -109,7 +109,7 @@ struct omo_ctx {
     // but no key time, so the item list of one gradient is the next one's too)
     std::vector<double> sp_times; std::vector<int> sp_free; int sp_begin = -1, sp_count = -1; bool sp_valid = false, sp_uploaded = false;
     std::vector<int> free_uploaded;
-    std::vector<double> h_cols;
+    double* h_grad = nullptr; size_t h_grad_cap = 0;   // pinned staging of omo_eval_grad: x [D] in, the 2F+1 column values out
 
     // single-candidate call (the NLopt callback, core_opt.cpp:42-57): H2D of x -> prepare -> objective -> finish -> D2H of f and
     // the three terms, captured once as a CUDA graph and replayed with one launch while nothing the capture baked in has changed
@@ -861,6 +861,7 @@ void omo_destroy(omo_ctx* ctx)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (ctx->sg_exec) cudaGraphExecDestroy(ctx->sg_exec);
     if (ctx->h_single) cudaFreeHost(ctx->h_single);
+    if (ctx->h_grad) cudaFreeHost(ctx->h_grad);
     if (ctx->d_single) cudaFree(ctx->d_single);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -1207,7 +1208,17 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     if ((st = ensure_capacity(ctx, col_count)) != OMO_OK) return st;
     if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
     if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; ctx->free_uploaded.clear(); }
-    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    {   // through pinned staging: a pageable source makes the copy a blocking staged one
+        const size_t need = (size_t)ctx->D + (size_t)(2 * F + 1);
+        if (need > ctx->h_grad_cap) {
+            if (ctx->h_grad) { OMO_CUDA(cudaStreamSynchronize(ctx->stream)); cudaFreeHost(ctx->h_grad); ctx->h_grad = nullptr; }
+            OMO_CUDA(cudaHostAlloc((void**)&ctx->h_grad, need * sizeof(double), cudaHostAllocDefault));
+            ctx->h_grad_cap = need;
+        }
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // an earlier asynchronous call may still be reading the staging buffer
+        std::memcpy(ctx->h_grad, x, (size_t)ctx->D * sizeof(double));
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, ctx->h_grad, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    }
     if (F > 0 && (ctx->free_uploaded.size() != (size_t)F || !std::equal(ctx->free_uploaded.begin(), ctx->free_uploaded.end(), free_idx))) {
         ctx->free_uploaded.assign(free_idx, free_idx + F);
         OMO_CUDA(cudaMemcpyAsync(ctx->d_free, ctx->free_uploaded.data(), (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
@@ -1271,11 +1282,11 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, P + 1)) != OMO_OK) return st;   // + the base row of the sparse evaluation: d_f must not move below
     if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
-    ctx->h_cols.resize(P);
-    OMO_CUDA(cudaMemcpyAsync(ctx->h_cols.data(), ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    double* cols = ctx->h_grad + ctx->D;   // pinned (sized by omo_eval_grad_columns above for this F)
+    OMO_CUDA(cudaMemcpyAsync(cols, ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
-    return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
+    if (fpm_out) std::copy(cols + 1, cols + P, fpm_out);
+    return omo_grad_from_columns(cols, F, h, f0_out, grad_out);
 }
 
 omo_status omo_grad_sparsity(const omo_ctx* ctx, unsigned long long* out2)
