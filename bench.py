@@ -252,11 +252,25 @@ def run_ours(args):
             ms = float(t.item())
         return ms, wall, kt, launches
 
+    Xfp = Fp2 = None
+    if not grad:   # the same candidates as their free entries only (omo_eval_free: expansion over x0 on the device)
+        Xfp = eng.pinned_array((B, idx.size))
+        Xfp[:] = X[:, idx]
+        Fp2 = eng.pinned_array((B,))
+
+    def step_e2e_free():
+        eng.eval_free_host_ptr(x0, idx, Xfp.ctypes.data, B, Fp2.ctypes.data)
+        if world > 1:
+            dist.barrier()
+
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
     ms_dev, wall_dev, (k_ms, k_n), launches = timed(step_device, args.steps, args.warmup, kernel_timing=True)
     ms_e2e, wall_e2e, _, _ = timed(step_e2e, args.steps, max(args.warmup, 3))
+    ms_free = None
+    if not grad:
+        ms_free, _, _, _ = timed(step_e2e_free, args.steps, max(args.warmup, 3))
     if sampler:
         sampler.stop_flag.set()
         sampler.join(timeout=2)
@@ -264,6 +278,8 @@ def run_ours(args):
     # correctness of what was timed: device-resident and host paths agree bit for bit
     f_dev = dF.cpu().numpy()
     assert np.array_equal(f_dev, np.asarray(Fp)), "device-resident and host-buffer paths disagree"
+    if Fp2 is not None:
+        assert np.array_equal(f_dev, np.asarray(Fp2)), "free-parameter and full-descriptor host paths disagree"
 
     if rank != 0:
         if world > 1:
@@ -350,6 +366,9 @@ def run_ours(args):
                    "l2": "flushed between timed iterations (256 MiB memset)", "gather": "nccl all_gather of f" if world > 1 else "none"},
         "clocks": sampler.summary() if sampler else None,
         "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int((8 * D + 4 * idx.size) if grad else B * D * 8), "d2h_bytes_per_step": int(B * 8)},
+        "e2e_free_parameters": None if ms_free is None else {
+            "value": n_total / (ms_free * 1e-3), "unit": UNIT, "ms_per_step": ms_free, "api": "omo_eval_free (candidates as their F free entries, expanded on the device)",
+            "h2d_bytes_per_step": int(B * idx.size * 8 + D * 8 + idx.size * 4), "d2h_bytes_per_step": int(B * 8)},
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu,
         "executed_fraction_of_dense_sample_evals": executed_frac,

@@ -123,6 +123,13 @@ omo_status omo_get_p_original(omo_ctx* ctx, double* p_out /* [N_s * 3J], sample-
 /* B candidates, X row-major [B][D] in HOST memory. f_out[B]; terms_out[B] optional (NULL). */
 omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_terms* terms_out);
 
+/* The same for candidates given in the callback's own parameter space (EvaluateObjective, OptiMo/core_opt.cpp:42-57, receives the
+ * F free entries and expands them over x_initial through the select / revert maps of core_opt.cpp:99-121): row b of Xfree[B][F]
+ * replaces entries free_idx[0..F) of x_base[D]; the expansion runs on the device, so only 8 B F bytes cross PCIe instead of
+ * 8 B D (the reference's default freezes t and v of every control point: F = 0.6 D). Bit-identical to omo_eval on the expanded rows. */
+omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx, int F, const double* Xfree, int B, double* f_out,
+                         omo_terms* terms_out);
+
 /* Same with X, f_out (and optional terms_out, 3 doubles per candidate) already in DEVICE memory of ctx's
  * device. Asynchronous on the ctx stream unless `sync` != 0. */
 omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync);

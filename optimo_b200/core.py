@@ -129,6 +129,7 @@ _OMO_SIG = {
     "omo_get_cost_weights": (ci, [_vp, _dp]),
     "omo_get_p_original": (ci, [_vp, _dp]),
     "omo_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
+    "omo_eval_free": (ci, [_vp, _dp, _ip, ci, _dp, ci, _dp, _dp]),
     "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
     "omo_eval_grad_columns": (ci, [_vp, _dp, _ip, ci, cd, ci, ci, _vp, ci]),
@@ -236,6 +237,23 @@ class Engine:
     def eval_host_ptr(self, x_ptr, B, f_ptr):
         """omo_eval on caller-owned (e.g. pinned) host buffers given as integer addresses."""
         self._ck(_omo.omo_eval(self.h, C.cast(x_ptr, _dp), B, C.cast(f_ptr, _dp), None), "omo_eval")
+
+    def eval_free(self, x_base, free_idx, Xfree, want_terms=False):
+        """omo_eval_free: candidates given by their free entries only (the callback's own parameter space)."""
+        xb, xbp = _d(x_base)
+        idx, ip = _i(free_idx)
+        Xf = np.ascontiguousarray(Xfree, dtype=np.float64).reshape(-1, idx.size)
+        f = np.zeros(Xf.shape[0])
+        terms = np.zeros((Xf.shape[0], 3)) if want_terms else None
+        self._ck(_omo.omo_eval_free(self.h, xbp, ip, idx.size, Xf.ctypes.data_as(_dp), Xf.shape[0], f.ctypes.data_as(_dp),
+                                    terms.ctypes.data_as(_dp) if want_terms else None), "omo_eval_free")
+        return (f, terms) if want_terms else f
+
+    def eval_free_host_ptr(self, x_base, free_idx, xf_ptr, B, f_ptr):
+        """omo_eval_free on caller-owned (e.g. pinned) host buffers given as integer addresses."""
+        xb, xbp = _d(x_base)
+        idx, ip = _i(free_idx)
+        self._ck(_omo.omo_eval_free(self.h, xbp, ip, idx.size, C.cast(xf_ptr, _dp), B, C.cast(f_ptr, _dp), None), "omo_eval_free")
 
     def eval_device(self, dX, B, dF, dTerms=None, sync=True):
         self._ck(_omo.omo_eval_device(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device")

@@ -109,7 +109,9 @@ struct omo_ctx {
     // but no key time, so the item list of one gradient is the next one's too)
     std::vector<double> sp_times; std::vector<int> sp_free; int sp_begin = -1, sp_count = -1; bool sp_valid = false, sp_uploaded = false;
     std::vector<int> free_uploaded;
-    double* h_grad = nullptr; size_t h_grad_cap = 0;   // pinned staging of omo_eval_grad: x [D] in, the 2F+1 column values out
+    std::vector<double> h_cols;
+    double* d_Xfree = nullptr; size_t xfree_cap = 0;   // omo_eval_free: the candidates' free entries as they arrive from the host
+    int* d_inv_free = nullptr; std::vector<int> inv_free_of;   // descriptor index -> position in the free list (-1: frozen), and the free list it was built from
 
     // single-candidate call (the NLopt callback, core_opt.cpp:42-57): H2D of x -> prepare -> objective -> finish -> D2H of f and
     // the three terms, captured once as a CUDA graph and replayed with one launch while nothing the capture baked in has changed
@@ -811,6 +813,71 @@ omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, 
     return launch_objective(ctx, P, B, fk, false, d_f, d_terms);
 }
 
+// Host rows of width W (W = D: whole candidates into d_X; W = F with `expand`: free entries into d_Xfree, expanded on the device)
+// copied and evaluated chunk by chunk; f (and the terms) copied back; synchronised on return.
+omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, double* d_stage, bool expand, int F, double* f_out, omo_terms* terms_out)
+{
+    omo_status st;
+    // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
+    // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
+    const size_t bytes = (size_t)B * W * sizeof(double);
+    // a chunk is at least 4 MB and at least ~8 waves of objective blocks
+    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 4736;
+    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));   // 4 measured best on stick240 (1.26 ms; 2: 1.30, 8: 1.33)
+    if (const char* e = std::getenv("OMO_EVAL_CHUNKS")) n_chunks = std::max(1, std::min(8, std::min(B, std::atoi(e))));
+    auto evaluate = [&](int b0, int nb) -> omo_status {
+        if (expand) {
+            const long long n = (long long)nb * ctx->D;
+            omo::expand_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_inv_free, ctx->D, F, d_stage + (size_t)b0 * W,
+                                                                                   ctx->d_X + (size_t)b0 * ctx->D, n);
+            OMO_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+        }
+        return eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, ctx->d_f + b0, terms_out ? ctx->d_terms + (size_t)3 * b0 : nullptr);
+    };
+    if (n_chunks == 1) {
+        OMO_CUDA(cudaMemcpyAsync(d_stage, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        if ((st = evaluate(0, B)) != OMO_OK) return st;
+    } else {
+        if (!ctx->copy_stream) {
+            OMO_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+            for (auto& e : ctx->chunk_ev) OMO_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            OMO_CUDA(cudaEventCreateWithFlags(&ctx->done_ev, cudaEventDisableTiming));
+        }
+        // d_X may still be read by kernels queued earlier on `stream`
+        OMO_CUDA(cudaEventRecord(ctx->done_ev, ctx->stream));
+        OMO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->done_ev, 0));
+        // Chunk sizes 1 : 2 : 2 : ... -- the kernels cannot start before the first chunk has landed, so it is half a chunk; the
+        // rest are equal because on this box the copy (~25 GB/s) takes about as long as the evaluation, and the step then ends
+        // one chunk's evaluation after the last copy. OMO_EVAL_CHUNKS_SHAPE=equal | ramp (default) | double (1 : 2 : 4 : ...).
+        int bound[9];
+        const char* shape = std::getenv("OMO_EVAL_CHUNKS_SHAPE");
+        const int mode_c = !shape ? 1 : (std::strcmp(shape, "equal") == 0 ? 0 : (std::strcmp(shape, "double") == 0 ? 2 : 1));
+        for (int c = 0; c <= n_chunks; ++c) {
+            long long num = c, den = n_chunks;
+            if (mode_c == 1) { num = c == 0 ? 0 : 2 * c - 1; den = 2 * n_chunks - 1; }
+            if (mode_c == 2) { num = (1LL << c) - 1; den = (1LL << n_chunks) - 1; }
+            bound[c] = (int)((long long)B * num / den);
+        }
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b0 = bound[c], nb = bound[c + 1] - b0;
+            if (nb <= 0) continue;
+            OMO_CUDA(cudaMemcpyAsync(d_stage + (size_t)b0 * W, X + (size_t)b0 * W, (size_t)nb * W * sizeof(double), cudaMemcpyHostToDevice, ctx->copy_stream));
+            OMO_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
+        }
+        for (int c = 0; c < n_chunks; ++c) {
+            const int b0 = bound[c], nb = bound[c + 1] - b0;
+            if (nb <= 0) continue;
+            OMO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0));
+            if ((st = evaluate(b0, nb)) != OMO_OK) return st;
+        }
+    }
+    OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
+
 }  // namespace
 
 // =====================================================================================================
@@ -861,7 +928,8 @@ void omo_destroy(omo_ctx* ctx)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (ctx->sg_exec) cudaGraphExecDestroy(ctx->sg_exec);
     if (ctx->h_single) cudaFreeHost(ctx->h_single);
-    if (ctx->h_grad) cudaFreeHost(ctx->h_grad);
+    if (ctx->d_Xfree) cudaFree(ctx->d_Xfree);
+    if (ctx->d_inv_free) cudaFree(ctx->d_inv_free);
     if (ctx->d_single) cudaFree(ctx->d_single);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
@@ -989,13 +1057,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
-    // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
-    // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
     const size_t bytes = (size_t)B * ctx->D * sizeof(double);
-    // a chunk is at least 4 MB and at least ~8 waves of objective blocks
-    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 4736;
-    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));   // 4 measured best on stick240 (1.26 ms; 2: 1.30, 8: 1.33)
-    if (const char* e = std::getenv("OMO_EVAL_CHUNKS")) n_chunks = std::max(1, std::min(8, std::min(B, std::atoi(e))));
     if (ctx->graph_mode < 0) { const char* e = std::getenv("OMO_GRAPH"); ctx->graph_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
     if (B == 1 && ctx->graph_mode == 1 && !ctx->timing) {
         // The solver's callback: one candidate per call, thousands of calls. The first call with a given state runs the plain
@@ -1039,49 +1101,30 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
         }
         ctx->sg_pending = key;
     }
-    if (n_chunks == 1) {
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_X, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
-        if ((st = eval_device_impl(ctx, ctx->d_X, B, ctx->d_f, terms_out ? ctx->d_terms : nullptr)) != OMO_OK) return st;
-    } else {
-        if (!ctx->copy_stream) {
-            OMO_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-            for (auto& e : ctx->chunk_ev) OMO_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-            OMO_CUDA(cudaEventCreateWithFlags(&ctx->done_ev, cudaEventDisableTiming));
-        }
-        // d_X may still be read by kernels queued earlier on `stream`
-        OMO_CUDA(cudaEventRecord(ctx->done_ev, ctx->stream));
-        OMO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->done_ev, 0));
-        // Chunk sizes 1 : 2 : 2 : ... -- the kernels cannot start before the first chunk has landed, so it is half a chunk; the
-        // rest are equal because on this box the copy (~25 GB/s) takes about as long as the evaluation, and the step then ends
-        // one chunk's evaluation after the last copy. OMO_EVAL_CHUNKS_SHAPE=equal | ramp (default) | double (1 : 2 : 4 : ...).
-        int bound[9];
-        const char* shape = std::getenv("OMO_EVAL_CHUNKS_SHAPE");
-        const int mode_c = !shape ? 1 : (std::strcmp(shape, "equal") == 0 ? 0 : (std::strcmp(shape, "double") == 0 ? 2 : 1));
-        for (int c = 0; c <= n_chunks; ++c) {
-            long long num = c, den = n_chunks;
-            if (mode_c == 1) { num = c == 0 ? 0 : 2 * c - 1; den = 2 * n_chunks - 1; }
-            if (mode_c == 2) { num = (1LL << c) - 1; den = (1LL << n_chunks) - 1; }
-            bound[c] = (int)((long long)B * num / den);
-        }
-        for (int c = 0; c < n_chunks; ++c) {
-            const int b0 = bound[c], nb = bound[c + 1] - b0;
-            if (nb <= 0) continue;
-            OMO_CUDA(cudaMemcpyAsync(ctx->d_X + (size_t)b0 * ctx->D, X + (size_t)b0 * ctx->D, (size_t)nb * ctx->D * sizeof(double),
-                                     cudaMemcpyHostToDevice, ctx->copy_stream));
-            OMO_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
-        }
-        for (int c = 0; c < n_chunks; ++c) {
-            const int b0 = bound[c], nb = bound[c + 1] - b0;
-            if (nb <= 0) continue;
-            OMO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0));
-            if ((st = eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, ctx->d_f + b0, terms_out ? ctx->d_terms + (size_t)3 * b0 : nullptr)) != OMO_OK)
-                return st;
-        }
+    return eval_host_pipelined(ctx, X, B, ctx->D, ctx->d_X, false, 0, f_out, terms_out);
+}
+
+omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx, int F, const double* Xfree, int B, double* f_out, omo_terms* terms_out)
+{
+    if (!ctx || (!x_base && ctx->D > 0) || F < 0 || (F > 0 && (!free_idx || !Xfree)) || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
+    if (B == 0) return OMO_OK;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
+    if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
+    if ((size_t)B * F > ctx->xfree_cap) { if ((st = dev_alloc(ctx, &ctx->d_Xfree, (size_t)B * F)) != OMO_OK) return st; ctx->xfree_cap = (size_t)B * F; }
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x_base, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    // descriptor index -> position in the free list: the expansion is then one gather per element, parallel over the whole batch
+    if (!ctx->d_inv_free || ctx->inv_free_of.size() != (size_t)F || !std::equal(ctx->inv_free_of.begin(), ctx->inv_free_of.end(), free_idx)) {
+        std::vector<int> inv((size_t)std::max(ctx->D, 1), -1);
+        for (int k = 0; k < F; ++k) inv[free_idx[k]] = k;          // a repeated index: the last entry wins, as a serial scatter would
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if ((st = upload(ctx, &ctx->d_inv_free, inv)) != OMO_OK) return st;
+        ctx->inv_free_of.assign(free_idx, free_idx + F);
     }
-    OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
-    return OMO_OK;
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // x_base and the map came from pageable memory
+    return eval_host_pipelined(ctx, Xfree, B, F, ctx->d_Xfree, true, F, f_out, terms_out);
 }
 
 omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd, double* qdd,
@@ -1208,17 +1251,7 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     if ((st = ensure_capacity(ctx, col_count)) != OMO_OK) return st;
     if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
     if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; ctx->free_uploaded.clear(); }
-    {   // through pinned staging: a pageable source makes the copy a blocking staged one
-        const size_t need = (size_t)ctx->D + (size_t)(2 * F + 1);
-        if (need > ctx->h_grad_cap) {
-            if (ctx->h_grad) { OMO_CUDA(cudaStreamSynchronize(ctx->stream)); cudaFreeHost(ctx->h_grad); ctx->h_grad = nullptr; }
-            OMO_CUDA(cudaHostAlloc((void**)&ctx->h_grad, need * sizeof(double), cudaHostAllocDefault));
-            ctx->h_grad_cap = need;
-        }
-        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // an earlier asynchronous call may still be reading the staging buffer
-        std::memcpy(ctx->h_grad, x, (size_t)ctx->D * sizeof(double));
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, ctx->h_grad, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    }
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     if (F > 0 && (ctx->free_uploaded.size() != (size_t)F || !std::equal(ctx->free_uploaded.begin(), ctx->free_uploaded.end(), free_idx))) {
         ctx->free_uploaded.assign(free_idx, free_idx + F);
         OMO_CUDA(cudaMemcpyAsync(ctx->d_free, ctx->free_uploaded.data(), (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
@@ -1282,11 +1315,11 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, P + 1)) != OMO_OK) return st;   // + the base row of the sparse evaluation: d_f must not move below
     if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
-    double* cols = ctx->h_grad + ctx->D;   // pinned (sized by omo_eval_grad_columns above for this F)
-    OMO_CUDA(cudaMemcpyAsync(cols, ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->h_cols.resize(P);
+    OMO_CUDA(cudaMemcpyAsync(ctx->h_cols.data(), ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (fpm_out) std::copy(cols + 1, cols + P, fpm_out);
-    return omo_grad_from_columns(cols, F, h, f0_out, grad_out);
+    if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
+    return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
 }
 
 omo_status omo_grad_sparsity(const omo_ctx* ctx, unsigned long long* out2)

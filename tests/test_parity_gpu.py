@@ -449,3 +449,22 @@ def test_maximum_joint_count_and_empty_inputs(oracle_port, shape):
         fs = cs.CalculateFullObjective(*cs.window, xs, xs)
         fo, _ = os_.full_objective(xs, xs)
         assert abs(fs - fo) <= 1e-9 * abs(fo) + 1e-18, (fs, fo)
+
+
+def test_free_parameter_batch_equals_expanded_batch():
+    """omo_eval_free (candidates as their F free entries, expanded on the device like EvaluateObjective's revert map,
+    core_opt.cpp:99-121) against omo_eval on the host-expanded rows: bit for bit, small and chunked batches."""
+    scene = synthetic.stick_240(load_scene("stick-figure"))
+    c = Core(scene)
+    c.UpdateGlobalWeight(2.0)
+    x0 = c.GetDescriptor()
+    idx = c.free_indices()
+    lo, hi = c.window
+    eng = c.engine(synced_window=(lo, hi))
+    for B in (1, 7, 1500):                       # 1500 x 468 doubles = 5.6 MB -> the pipelined, chunked path
+        X = synthetic.perturbed_candidates(x0, B)
+        f_full, t_full = eng.eval(X, want_terms=True)
+        f_free, t_free = eng.eval_free(x0, idx, X[:, idx], want_terms=True)
+        assert np.array_equal(f_full, f_free) and np.array_equal(t_full, t_free), B
+    with pytest.raises(EngineError):
+        eng.eval_free(x0, np.array([x0.size], dtype=np.int32), np.zeros((1, 1)))
