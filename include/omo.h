@@ -174,6 +174,37 @@ omo_status omo_grad_from_columns(const double* f_cols, int F, double h, double* 
 /* Contiguous shard [begin, begin+count) of n items for `rank` of `world` (first ranks take the remainder). */
 void omo_shard_range(int n, int rank, int world, int* begin, int* count);
 
+/* ---- multi-device engine: ONE host thread, several GPUs of one box ---------
+ * The reference's callback runs on one thread of one process (NLopt's serial loop, OptiMo/core_opt.cpp:141-152; its only
+ * parallel construct is the parallel_for of Core::SetStates, OptiMo/core_rbdl.cpp:157-161). An omo_multi lets that one
+ * thread use every GPU: it owns one omo_ctx per device, a worker thread per device, the pinned gather buffer and the NCCL
+ * communicators. Batches are sharded over candidates, gradients over their 2F+1 finite-difference columns
+ * (omo_shard_range); scene, weights and x_original are replicated; the only exchange is the gather of one double per
+ * candidate / column. Results are bit-identical to the single-device entry points of the same names.
+ * device_ids == NULL: devices 0 .. n_dev-1; n_dev <= 0: every visible device. Not re-entrant (one caller at a time). */
+typedef struct omo_multi omo_multi;
+#define OMO_GATHER_HOST 0 /* every device copies its slice into the host array itself (default) */
+#define OMO_GATHER_NCCL 1 /* ncclAllGather over NVLink / NVSwitch, then one device-to-host copy */
+omo_status omo_create_multi(const omo_scene_desc* scene, const int* device_ids, int n_dev, omo_multi** out);
+void omo_destroy_multi(omo_multi* m);
+const char* omo_multi_last_error(const omo_multi* m); /* m may be NULL: error of the last failed omo_create_multi */
+int omo_multi_num_devices(const omo_multi* m);
+int omo_multi_device(const omo_multi* m, int i);      /* CUDA device index of slot i */
+omo_ctx* omo_multi_ctx(omo_multi* m, int i);          /* the engine of slot i (queries only while no multi call runs) */
+/* OMO_NCCL_ERROR when libnccl cannot be loaded or the communicators cannot be created. Env OMO_GATHER=nccl selects it at creation. */
+omo_status omo_multi_set_gather(omo_multi* m, int mode);
+int omo_multi_get_gather(const omo_multi* m);
+omo_status omo_multi_set_window(omo_multi* m, double min_t, double max_t, double dt);
+omo_status omo_multi_set_weights(omo_multi* m, const double* w_param, int D, double w_traj, const omo_gauss* kernels, int n_kernels, int cyclic);
+omo_status omo_multi_set_original(omo_multi* m, const double* x_original, int D);
+/* omo_eval / omo_eval_free with the B candidates split over the devices; every device writes its slice of f_out / terms_out. */
+omo_status omo_multi_eval(omo_multi* m, const double* X, int B, double* f_out, omo_terms* terms_out);
+omo_status omo_multi_eval_free(omo_multi* m, const double* x_base, const int* free_idx, int F, const double* Xfree, int B, double* f_out,
+                               omo_terms* terms_out);
+/* omo_eval_grad with the 2F+1 columns split over the devices (omo_eval_grad_columns per device + gather + omo_grad_from_columns). */
+omo_status omo_multi_eval_grad(omo_multi* m, const double* x, const int* free_idx, int F, double h, double* f0_out, double* grad_out,
+                               double* fpm_out);
+
 /* ---- device helpers for harnesses (no reference counterpart) ---------------------------------------- */
 omo_status omo_device_alloc(omo_ctx* ctx, unsigned long long bytes, void** out);
 omo_status omo_device_free(omo_ctx* ctx, void* p);

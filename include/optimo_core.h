@@ -26,6 +26,9 @@ int optimo_read_json_string(void* h, const char* text);   /* Core::ApplyJsonToSc
 int optimo_write_json(void* h, const char* path);         /* Core::WriteJson, core_io.cpp:165-169 */
 int optimo_scene_json(void* h, char* out, int cap);       /* ConvertCurrentSceneToJson; returns the length */
 int optimo_set_device(void* h, int device);
+/* Several GPUs of one box behind the same calls: batches are sharded over candidates, gradients over their finite-difference
+ * columns (include/omo.h: omo_multi). n <= 1 goes back to one device. */
+int optimo_set_devices(void* h, const int* devices, int n);
 
 int optimo_min_frame(void* h);
 int optimo_max_frame(void* h);
@@ -84,7 +87,9 @@ void optimo_record_solve_trace(void* h, int enable);
 int optimo_solve_trace_size(void* h, int* rows, int* dim);
 int optimo_get_solve_trace(void* h, double* out);
 
-int optimo_cache_size(void* h, int* n_samples, int* dof); /* Core::GetOptimizationCache, core.h:134-144 */
+/* Core::GetOptimizationCache, core.h:134-144 (thread-safe copy). optimo_cache_size takes the copy and keeps it for the calling
+ * thread; optimo_get_cache reads arrays of THAT copy, so one read-out never mixes two evaluations. */
+int optimo_cache_size(void* h, int* n_samples, int* dof);
 int optimo_get_cache(void* h, int which, double* out);    /* 0 time, 1 q, 2 q_dot, 3 q_ddot, 4 tau, 5 local_cost */
 void optimo_clear_optimization_cache(void* h);
 
@@ -103,6 +108,7 @@ int optimo_write_history(void* h, const char* path);                  /* core_io
 
 void* optimo_engine(void* h);                                   /* the omo_ctx* behind this Core (include/omo.h) */
 void* optimo_engine_synced(void* h, double min_t, double max_t); /* same, after pushing window/weights/x_original */
+void* optimo_engine_multi(void* h);                             /* the omo_multi* behind this Core, NULL unless optimo_set_devices named >= 2 */
 
 #ifdef __cplusplus
 }

@@ -61,6 +61,7 @@ _CORE_SIG = {
     "optimo_write_json": (ci, [_vp, cs]),
     "optimo_scene_json": (ci, [_vp, C.c_char_p, ci]),
     "optimo_set_device": (ci, [_vp, ci]),
+    "optimo_set_devices": (ci, [_vp, _ip, ci]),
     "optimo_min_frame": (ci, [_vp]),
     "optimo_max_frame": (ci, [_vp]),
     "optimo_set_frames": (None, [_vp, ci, ci]),
@@ -113,6 +114,7 @@ _CORE_SIG = {
     "optimo_clear_optimization_cache": (None, [_vp]),
     "optimo_engine": (_vp, [_vp]),
     "optimo_engine_synced": (_vp, [_vp, cd, cd]),
+    "optimo_engine_multi": (_vp, [_vp]),
 }
 for _n, (_r, _a) in _CORE_SIG.items():
     _sig(_core, _n, _r, _a)
@@ -151,6 +153,16 @@ _OMO_SIG = {
     "omo_selftest_division": (ci, [_vp, _dp, _dp, ci, _dp, _dp, _ip]),
     "omo_grad_sparsity": (ci, [_vp, C.POINTER(_ull)]),
     "omo_graph_replays": (_ull, [_vp]),
+    "omo_multi_last_error": (cs, [_vp]),
+    "omo_multi_num_devices": (ci, [_vp]),
+    "omo_multi_device": (ci, [_vp, ci]),
+    "omo_multi_ctx": (_vp, [_vp, ci]),
+    "omo_multi_set_gather": (ci, [_vp, ci]),
+    "omo_multi_get_gather": (ci, [_vp]),
+    "omo_multi_set_window": (ci, [_vp, cd, cd, cd]),
+    "omo_multi_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
+    "omo_multi_eval_free": (ci, [_vp, _dp, _ip, ci, _dp, ci, _dp, _dp]),
+    "omo_multi_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
 }
 for _n, (_r, _a) in _OMO_SIG.items():
     _sig(_omo, _n, _r, _a)
@@ -355,15 +367,74 @@ class Engine:
         return v.value
 
 
+class MultiEngine:
+    """Raw view of an omo_multi* (include/omo.h) owned by a Core: one host thread, several GPUs of one box."""
+
+    GATHER_HOST, GATHER_NCCL = 0, 1
+
+    def __init__(self, handle):
+        if not handle:
+            raise EngineError("multi-device engine is not available: " + (_core.optimo_last_error() or b"").decode())
+        self.h = handle
+
+    def _ck(self, st, what):
+        if st != 0:
+            raise EngineError(f"{what}: status {st}: {(_omo.omo_multi_last_error(self.h) or b'').decode()}")
+
+    @property
+    def num_devices(self):
+        return _omo.omo_multi_num_devices(self.h)
+
+    def devices(self):
+        return [_omo.omo_multi_device(self.h, i) for i in range(self.num_devices)]
+
+    def ctx(self, i):
+        return Engine(_omo.omo_multi_ctx(self.h, i))
+
+    def set_gather(self, mode):
+        self._ck(_omo.omo_multi_set_gather(self.h, int(mode)), "omo_multi_set_gather")
+
+    @property
+    def gather(self):
+        return _omo.omo_multi_get_gather(self.h)
+
+    def eval_host_ptr(self, x_ptr, B, f_ptr):
+        self._ck(_omo.omo_multi_eval(self.h, C.cast(x_ptr, _dp), B, C.cast(f_ptr, _dp), None), "omo_multi_eval")
+
+    def eval(self, X, want_terms=False):
+        X, xp = _d(X)
+        D = self.ctx(0).D
+        X2 = X.reshape(-1, D)
+        f = np.zeros(X2.shape[0])
+        terms = np.zeros((X2.shape[0], 3)) if want_terms else None
+        self._ck(_omo.omo_multi_eval(self.h, xp, X2.shape[0], f.ctypes.data_as(_dp), terms.ctypes.data_as(_dp) if want_terms else None), "omo_multi_eval")
+        return (f, terms) if want_terms else f
+
+    def eval_free_host_ptr(self, x_base, free_idx, xf_ptr, B, f_ptr):
+        xb, xbp = _d(x_base)
+        idx, ip = _i(free_idx)
+        self._ck(_omo.omo_multi_eval_free(self.h, xbp, ip, idx.size, C.cast(xf_ptr, _dp), B, C.cast(f_ptr, _dp), None), "omo_multi_eval_free")
+
+    def eval_grad(self, x, free_idx, h=1e-4):
+        x, xp = _d(x)
+        idx, ip = _i(free_idx)
+        g, fpm = np.zeros(idx.size), np.zeros((idx.size, 2))
+        f0 = C.c_double(0.0)
+        self._ck(_omo.omo_multi_eval_grad(self.h, xp, ip, idx.size, float(h), C.byref(f0), g.ctypes.data_as(_dp), fpm.ctypes.data_as(_dp)), "omo_multi_eval_grad")
+        return f0.value, g, fpm
+
+
 class Core:
     """Headless Core (one instance == one scene + one lazily created GPU engine)."""
 
-    def __init__(self, scene=None, device=None):
+    def __init__(self, scene=None, device=None, devices=None):
         self.h = _core.optimo_core_new()
         if not self.h:
             raise EngineError("optimo_core_new failed")
         if device is not None:
             self._ck(_core.optimo_set_device(self.h, int(device)))
+        if devices is not None:
+            self.SetDevices(devices)
         if scene is not None:
             if isinstance(scene, dict):
                 self.ReadJsonString(json.dumps(scene))
@@ -385,6 +456,14 @@ class Core:
         if rc == 2:
             raise ForcedStop(msg)
         raise EngineError(msg)
+
+    def SetDevices(self, devices):
+        """Several GPUs of one box behind the same calls (batches sharded over candidates, gradients over columns)."""
+        a, p = _i(list(devices))
+        self._ck(_core.optimo_set_devices(self.h, p, a.size))
+
+    def multi_engine(self):
+        return MultiEngine(_core.optimo_engine_multi(self.h))
 
     # ---- IO / structure ------------------------------------------------------------------------------
     def ReadJson(self, path):

@@ -24,6 +24,11 @@ namespace {
 std::string g_create_error;
 std::mutex g_scene_mutex;
 const omo_ctx* g_active_scene[64] = {nullptr};  // per device: whose table sits in c_scene
+// The table-driven kernels read ONE constant-memory scene table per device (c_scene). Every entry point that launches holds
+// its device's mutex from the upload of its table to its last launch, so two contexts on one device driven from two host
+// threads (two Cores) cannot read each other's table; a context that finds another one's table active waits for the device
+// to drain before it overwrites it (activate_scene). Contexts on different devices never contend.
+std::recursive_mutex g_device_mutex[64];
 
 constexpr int kBlockThreads = 128;
 
@@ -58,11 +63,13 @@ struct omo_ctx {
         size_t smem = 0, item_smem = 0;
         int sub = 1;
         int regs = 0;
+        bool from_disk = false, loop_form = false;
         unsigned long long uploaded_version = 0;
         double compile_ms = 0.0;
     };
     JitKernel jit[8];
     int jit_mode = -1;            // -1: auto (large launches), 0: never, 1: always (OMO_JIT)
+    bool prefer_jit = false;      // this launch takes the specialised kernel whatever its size (gradient columns: never by shard size)
     std::string jit_log;
     unsigned long long jit_launches = 0;
 
@@ -72,6 +79,7 @@ struct omo_ctx {
     std::vector<double> tgrid;
     int N_s = 0, n_tiles = 0, T_out = 0;
     double* d_tgrid = nullptr;
+    bool residues_valid = false; double residues_dt = 0.0;   // the stencil residues of constants depend on dt only
 
     // weights
     bool have_weights = false;
@@ -90,7 +98,7 @@ struct omo_ctx {
     bool p_orig_dirty = true;
 
     // work buffers (capacity in candidates)
-    int cap = 0;
+    int cap = 0, cap_tiles = 0;   // candidates / tiles per candidate the work buffers were sized for
     double *d_X = nullptr, *d_prep = nullptr, *d_dparam = nullptr, *d_partial = nullptr, *d_f = nullptr, *d_terms = nullptr;
     unsigned* d_flags = nullptr;
     double* d_seg = nullptr;              // [cap][n_cp][OMO_SEGD] prepared segments
@@ -141,6 +149,14 @@ namespace {
             return (e_ == cudaErrorMemoryAllocation) ? OMO_OOM : OMO_CUDA_ERROR;                           \
         }                                                                                                  \
     } while (0)
+
+struct DeviceLock {
+    std::recursive_mutex* m = nullptr;
+    explicit DeviceLock(const omo_ctx* ctx) { if (ctx && ctx->device >= 0 && ctx->device < 64) { m = &g_device_mutex[ctx->device]; m->lock(); } }
+    ~DeviceLock() { if (m) m->unlock(); }
+    DeviceLock(const DeviceLock&) = delete;
+    DeviceLock& operator=(const DeviceLock&) = delete;
+};
 
 omo_status fail(omo_ctx* ctx, omo_status st, const std::string& msg)
 {
@@ -402,8 +418,9 @@ int prep_parts(const omo_ctx* ctx) { return std::max(1, (ctx->n_cp + kPrepChunk 
 
 omo_status ensure_capacity(omo_ctx* ctx, int B)
 {
-    if (B <= ctx->cap) return OMO_OK;
-    const int cap = std::max(B, 16);
+    if (B <= ctx->cap && ctx->n_tiles <= ctx->cap_tiles) return OMO_OK;
+    const int cap = std::max(std::max(B, ctx->cap), 16);
+    const int tiles = std::max(std::max(ctx->n_tiles, ctx->cap_tiles), 1);
     omo_status st;
     if ((st = dev_alloc(ctx, &ctx->d_X, (size_t)cap * ctx->D)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_prep, (size_t)cap * 6 * ctx->n_cp)) != OMO_OK) return st;
@@ -411,11 +428,11 @@ omo_status ensure_capacity(omo_ctx* ctx, int B)
     if ((st = dev_alloc(ctx, &ctx->d_flags, (size_t)cap)) != OMO_OK) return st;
     // + OMO_SEGW records of slack: the staging copy of the last channel never reads past the allocation
     if ((st = dev_alloc(ctx, &ctx->d_seg, ((size_t)cap * ctx->n_cp + OMO_SEGW) * OMO_SEGD)) != OMO_OK) return st;
-    if ((st = dev_alloc(ctx, &ctx->d_tile_seg, (size_t)cap * std::max(ctx->n_tiles, 1) * std::max(ctx->hs.n_keyed, 1))) != OMO_OK) return st;
-    if ((st = dev_alloc(ctx, &ctx->d_partial, (size_t)cap * std::max(ctx->n_tiles, 1) * 2)) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_tile_seg, (size_t)cap * tiles * std::max(ctx->hs.n_keyed, 1))) != OMO_OK) return st;
+    if ((st = dev_alloc(ctx, &ctx->d_partial, (size_t)cap * tiles * 2)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_f, (size_t)cap)) != OMO_OK) return st;
     if ((st = dev_alloc(ctx, &ctx->d_terms, (size_t)cap * 3)) != OMO_OK) return st;
-    ctx->cap = cap;
+    ctx->cap = cap; ctx->cap_tiles = tiles;
     return OMO_OK;
 }
 
@@ -501,19 +518,26 @@ omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
     // device) skips NVRTC
     static std::mutex cache_mutex;
     static std::map<uint64_t, std::vector<char>> cubin_cache;
-    const uint64_t key = omo_jit::fnv1a(spec.source + "#sub" + std::to_string(spec.sub));
+    const uint64_t key = omo_jit::fnv1a(spec.source + "#sub" + std::to_string(spec.sub)) ^ omo_jit::headers_hash();
     std::vector<char> cubin;
     {
         std::lock_guard<std::mutex> g(cache_mutex);
         auto it = cubin_cache.find(key);
         if (it != cubin_cache.end()) cubin = it->second;
     }
-    if (cubin.empty()) {
-        std::string log;
-        if (!omo_jit::compile(spec.source, cubin, log, spec.sub)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+    if (cubin.empty() && omo_jit::disk_cache_load(key, cubin)) {
+        k.from_disk = true;
         std::lock_guard<std::mutex> g(cache_mutex);
         cubin_cache[key] = cubin;
     }
+    if (cubin.empty()) {
+        std::string log;
+        if (!omo_jit::compile(spec.source, cubin, log, spec.sub)) { ctx->jit_log = "NVRTC: " + log; return nullptr; }
+        omo_jit::disk_cache_store(key, cubin);
+        std::lock_guard<std::mutex> g(cache_mutex);
+        cubin_cache[key] = cubin;
+    }
+    k.loop_form = spec.loop_form;
     if (a.cuModuleLoadData(&k.mod, cubin.data()) != 0) { ctx->jit_log = "cuModuleLoadData failed"; return nullptr; }
     size_t bytes = 0;
     if (a.cuModuleGetFunction(&k.fn, k.mod, "omo_jit_kernel") != 0 || a.cuModuleGetGlobal(&k.d_scene, &bytes, k.mod, "c_scene") != 0 ||
@@ -575,7 +599,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     // large launches run the scene-specialised kernel (auto: >= 64 K sample-evals; OMO_JIT=1 always, OMO_JIT=0 never)
     const int mode = jit_mode(ctx);
     // (sparse column launches always do: a gradient's columns must not switch kernels with the size of a rank's shard)
-    if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || (long long)P.n_items * plan.t_out >= 65536)) {
+    if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || ctx->prefer_jit || (long long)P.n_items * plan.t_out >= 65536)) {
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
             if (d_item_map) return OMO_OK;
@@ -677,11 +701,10 @@ omo_status install_grid(omo_ctx* ctx, std::vector<double>& grid, double dt)
     ctx->T_out = (ctx->N_s + ctx->n_tiles - 1) / ctx->n_tiles;
     omo_status st = upload(ctx, &ctx->d_tgrid, ctx->tgrid);
     if (st != OMO_OK) return st;
-    refresh_residues(ctx);
+    if (!ctx->residues_valid || ctx->residues_dt != dt) { refresh_residues(ctx); ctx->residues_valid = true; ctx->residues_dt = dt; }
     ctx->wcost_dirty = true; ctx->p_orig_dirty = true;
     ctx->sp_valid = false;  // the sparse-gradient item lists are per time grid
-    ctx->cap = 0;  // partial[] depends on n_tiles
-    ctx->out_cap_samples = 0;
+    // work / output buffers are kept: ensure_capacity and ensure_outputs grow them when the new grid needs more tiles / samples
     return OMO_OK;
 }
 
@@ -734,9 +757,9 @@ omo_status ensure_ready(omo_ctx* ctx)
 // row `col_count`). A control point at chain position pos shapes the segments pos-1 -> pos and pos -> pos+1 of its channel
 // (curve.cpp:57-93: each segment reads its two end points only; before the first / after the last key the end value holds),
 // so a sample is affected iff T[pos-1] <= t < T[pos+1] (open ends at a channel's first / last point), and through the
-// 5-point stencils (core_rbdl.cpp:28-95) so are its +-2 neighbours. Returns false -- evaluate densely -- when that
-// reasoning does not hold: a chain of x is not time-sorted (list-order segment search), the perturbed field is the key
-// time itself, or a cyclic curve's end tangents are averaged.
+// 5-point stencils (core_rbdl.cpp:28-95) so are its +-2 neighbours. A column that moves a key time itself, or the averaged
+// end tangent of a cyclic curve, keeps all its tiles. Returns false -- evaluate densely -- only when a chain of x is not
+// time-sorted (list-order segment search) or the window has a single tile.
 bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, int col_begin, int col_count)
 {
     const int n_cp = ctx->n_cp, N = ctx->N_s, T_out = ctx->T_out, n_tiles = ctx->n_tiles;
@@ -763,14 +786,18 @@ bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, i
         if (col > 0) {
             const int idx = free_idx[(col - 1) >> 1], cp = idx / 5, field = idx % 5, pos = ctx->pos_of_cp[cp];
             const bool cyc_end = ctx->cyclic && field == 2 && (cp == ctx->first_of_pos[pos] || cp == ctx->last_of_pos[pos]);
-            if (field == 0 || cyc_end) return false;
-            const double t_lo = (pos > 0 && ctx->next_same[pos - 1]) ? x[5 * ctx->cp_of_pos[pos - 1]] : -INFINITY;
-            const double t_hi = ctx->next_same[pos] ? x[5 * ctx->cp_of_pos[pos + 1]] : INFINITY;
-            // samples with t_lo <= t <= t_hi, one sample of slack each side, then the stencil's two
-            const int s_lo = (int)(std::lower_bound(tg.begin(), tg.end(), t_lo) - tg.begin()) - 3;
-            const int s_hi = (int)(std::upper_bound(tg.begin(), tg.end(), t_hi) - tg.begin()) - 1 + 3;
-            if (s_hi < 0 || s_lo > N - 1) { lo = 1; hi = 0; }
-            else { lo = std::max(s_lo, 0) / T_out; hi = std::min(std::min(s_hi, N - 1) / T_out, n_tiles - 1); }
+            // A moved key time re-shapes the segment search, a cyclic curve's end tangent is shared by both ends: such a column
+            // keeps every tile (lo = 0, hi = n_tiles - 1) but stays in the item-map launch, so that f(x + h e_k) and f(x - h e_k)
+            // come from the same kernel whichever rank's shard they fall into.
+            if (!(field == 0 || cyc_end)) {
+                const double t_lo = (pos > 0 && ctx->next_same[pos - 1]) ? x[5 * ctx->cp_of_pos[pos - 1]] : -INFINITY;
+                const double t_hi = ctx->next_same[pos] ? x[5 * ctx->cp_of_pos[pos + 1]] : INFINITY;
+                // samples with t_lo <= t <= t_hi, one sample of slack each side, then the stencil's two
+                const int s_lo = (int)(std::lower_bound(tg.begin(), tg.end(), t_lo) - tg.begin()) - 3;
+                const int s_hi = (int)(std::upper_bound(tg.begin(), tg.end(), t_hi) - tg.begin()) - 1 + 3;
+                if (s_hi < 0 || s_lo > N - 1) { lo = 1; hi = 0; }
+                else { lo = std::max(s_lo, 0) / T_out; hi = std::min(std::min(s_hi, N - 1) / T_out, n_tiles - 1); }
+            }
         }
         ctx->h_lo[lc] = lo; ctx->h_hi[lc] = hi;
         for (int t = lo; t <= hi; ++t) ctx->h_items.push_back(lc * n_tiles + t);
@@ -1019,6 +1046,7 @@ omo_status omo_get_time_grid(const omo_ctx* ctx, double* t_out)
 omo_status omo_get_cost_weights(const omo_ctx* cctx, double* w_out)
 {
     omo_ctx* ctx = const_cast<omo_ctx*>(cctx);
+    DeviceLock device_lock(ctx);
     if (!ctx || !w_out) return OMO_BAD_ARG;
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
@@ -1028,6 +1056,7 @@ omo_status omo_get_cost_weights(const omo_ctx* cctx, double* w_out)
 
 omo_status omo_get_p_original(omo_ctx* ctx, double* p_out)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || !p_out) return OMO_BAD_ARG;
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
@@ -1041,6 +1070,7 @@ omo_status omo_get_p_original(omo_ctx* ctx, double* p_out)
 
 omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || !dX || !d_f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
     if (B == 0) return OMO_OK;
     omo_status st = ensure_ready(ctx);
@@ -1052,6 +1082,7 @@ omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_ou
 
 omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_terms* terms_out)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!X && ctx->D > 0) || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");   // D = 0: a scene without keyed curves
     if (B == 0) return OMO_OK;
     omo_status st = ensure_ready(ctx);
@@ -1106,6 +1137,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
 
 omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx, int F, const double* Xfree, int B, double* f_out, omo_terms* terms_out)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!x_base && ctx->D > 0) || F < 0 || (F > 0 && (!free_idx || !Xfree)) || !f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
     for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
     if (B == 0) return OMO_OK;
@@ -1130,6 +1162,7 @@ omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx
 omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd, double* qdd,
                            double* tau, double* local_cost)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!x && ctx->D > 0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
@@ -1150,6 +1183,7 @@ omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_ter
 
 omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!x && ctx->D > 0) || !p_out) return fail(ctx, OMO_BAD_ARG, "bad argument");
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
@@ -1164,6 +1198,7 @@ omo_status omo_positions(omo_ctx* ctx, const double* x, double* p_out)
 omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times, int M, double dt, double* q, double* qd,
                               double* qdd, double* tau, double* root_euler, double* p)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!x && ctx->D > 0) || M < 0 || (M > 0 && !times) || !(dt > 0.0)) return fail(ctx, OMO_BAD_ARG, "bad argument");
     if (!ctx->have_weights || !ctx->have_original) return fail(ctx, OMO_NOT_READY, "omo_set_weights / omo_set_original have not been called");
     if (M == 0) return OMO_OK;
@@ -1173,8 +1208,6 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
     std::vector<int> order(M);
     for (int i = 0; i < M; ++i) order[i] = i;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return times[a] < times[b]; });
-    const bool had_window = ctx->have_window;
-    const double w_min = ctx->min_t, w_max = ctx->max_t, w_dt = ctx->dt;
     const size_t dof = (size_t)3 * ctx->J;
     constexpr int kMaxTriples = 1 << 18;
     std::vector<char> done(M, 0);
@@ -1182,7 +1215,18 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
     std::vector<double> grid, h[6];
     int left = M;
     omo_status st = OMO_OK;
-    double* d_w = nullptr; double* d_root = nullptr;
+    double* d_w = nullptr; double* d_root = nullptr; double* d_grid = nullptr;
+    // The triples' grid is swapped in for the launches below and the objective window is put back untouched afterwards: its
+    // cost weights, p_original, sparse-gradient item lists, work buffers and the captured single-candidate graph all stay
+    // valid (a torque query from the UI thread in the middle of a solve costs its own launches and nothing else).
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::vector<double> saved_grid;
+    saved_grid.swap(ctx->tgrid);
+    double* const saved_d_tgrid = ctx->d_tgrid;
+    const int saved_N = ctx->N_s, saved_tiles = ctx->n_tiles, saved_T = ctx->T_out;
+    const double saved_dt = ctx->dt;
+    const bool swap_residues = ctx->residues_valid && ctx->residues_dt != dt;
+    if (!ctx->residues_valid || swap_residues) { ctx->dt = dt; refresh_residues(ctx); ctx->residues_valid = true; ctx->residues_dt = dt; }
     while (left > 0 && st == OMO_OK) {
         take.clear(); grid.clear();
         double last_end = -INFINITY;
@@ -1197,14 +1241,20 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
         }
         left -= (int)take.size();
         const int n = (int)take.size(), N = 3 * n;
-        ctx->have_window = false;
-        if ((st = install_grid(ctx, grid, dt)) != OMO_OK) break;
+        ctx->tgrid = grid;
+        ctx->N_s = N; ctx->dt = dt;
+        ctx->n_tiles = (N + kBlockThreads - 5) / (kBlockThreads - 4);
+        ctx->T_out = (N + ctx->n_tiles - 1) / ctx->n_tiles;
+        if ((st = dev_alloc(ctx, &d_grid, (size_t)N)) != OMO_OK) break;
+        ctx->d_tgrid = d_grid;
         if ((st = ensure_capacity(ctx, 1)) != OMO_OK) break;
         if ((st = ensure_outputs(ctx)) != OMO_OK) break;
         if ((st = dev_alloc(ctx, &d_w, (size_t)N)) != OMO_OK) break;
         if ((st = dev_alloc(ctx, &d_root, (size_t)N * 3)) != OMO_OK) break;
-        OMO_CUDA(cudaMemsetAsync(d_w, 0, (size_t)N * sizeof(double), ctx->stream));
-        OMO_CUDA(cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        cudaError_t ce = cudaMemcpyAsync(d_grid, grid.data(), (size_t)N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        if (ce == cudaSuccess) ce = cudaMemsetAsync(d_w, 0, (size_t)N * sizeof(double), ctx->stream);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+        if (ce != cudaSuccess) { st = fail(ctx, OMO_CUDA_ERROR, cudaGetErrorString(ce)); break; }
         if ((st = activate_scene(ctx)) != OMO_OK) break;
         if ((st = run_prepare(ctx, ctx->d_X, 1)) != OMO_OK) break;
         OmoEvalParams P;
@@ -1215,33 +1265,35 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
         // only the middle sample of each triple is read back (strided copies, row = one sample)
         double* outs[6] = {q, qd, qdd, tau, p, root_euler};
         const double* srcs[6] = {ctx->d_oq, ctx->d_oqd, ctx->d_oqdd, ctx->d_otau, ctx->d_op, d_root};
-        for (int a = 0; a < 6; ++a) {
+        for (int a = 0; a < 6 && ce == cudaSuccess; ++a) {
             if (!outs[a]) continue;
             const size_t w = (a == 5 ? 3 : dof) * sizeof(double);
             h[a].resize((size_t)n * (a == 5 ? 3 : dof));
-            OMO_CUDA(cudaMemcpy2DAsync(h[a].data(), w, srcs[a] + (a == 5 ? 3 : dof), 3 * w, w, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+            ce = cudaMemcpy2DAsync(h[a].data(), w, srcs[a] + (a == 5 ? 3 : dof), 3 * w, w, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
         }
-        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
+        if (ce != cudaSuccess) { st = fail(ctx, OMO_CUDA_ERROR, cudaGetErrorString(ce)); break; }
         for (int a = 0; a < 6; ++a) {
             if (!outs[a]) continue;
             const size_t w = (a == 5 ? 3 : dof);
             for (int k = 0; k < n; ++k) std::memcpy(outs[a] + (size_t)take[k] * w, h[a].data() + (size_t)k * w, w * sizeof(double));
         }
     }
+    cudaStreamSynchronize(ctx->stream);
     if (d_w) cudaFree(d_w);
     if (d_root) cudaFree(d_root);
-    // put the objective window back (p_original and the cost weights are rebuilt on the next evaluation)
-    ctx->have_window = false;
-    if (had_window) {
-        const omo_status st2 = omo_set_window(ctx, w_min, w_max, w_dt);
-        if (st == OMO_OK) st = st2;
-    }
+    if (d_grid) cudaFree(d_grid);
+    // put the objective window back exactly as it was
+    ctx->tgrid.swap(saved_grid);
+    ctx->d_tgrid = saved_d_tgrid; ctx->N_s = saved_N; ctx->n_tiles = saved_tiles; ctx->T_out = saved_T; ctx->dt = saved_dt;
+    if (swap_residues) { refresh_residues(ctx); ctx->residues_dt = saved_dt; }
     return st;
 }
 
 omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, int col_begin, int col_count,
                                  double* d_f_cols, int sync)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx || (!x && ctx->D > 0) || (F > 0 && !free_idx) || F < 0 || !d_f_cols) return fail(ctx, OMO_BAD_ARG, "bad argument");
     if (col_begin < 0 || col_count < 0 || col_begin + col_count > 2 * F + 1) return fail(ctx, OMO_BAD_ARG, "column range outside [0, 2F+1)");
     for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
@@ -1267,7 +1319,10 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
     if (!sparse) {
-        if ((st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr)) != OMO_OK) return st;
+        ctx->prefer_jit = true;    // same kernel as the sparse columns of the other shards
+        st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr);
+        ctx->prefer_jit = false;
+        if (st != OMO_OK) return st;
     } else {
         if (ctx->h_items.size() > ctx->items_cap) {
             if ((st = dev_alloc(ctx, &ctx->d_items, ctx->h_items.size())) != OMO_OK) return st;
@@ -1309,6 +1364,7 @@ omo_status omo_grad_from_columns(const double* f_cols, int F, double h, double* 
 
 omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, double* f0_out, double* grad_out, double* fpm_out)
 {
+    DeviceLock device_lock(ctx);
     if (!ctx) return OMO_BAD_ARG;
     const int P = 2 * F + 1;
     omo_status st = ensure_ready(ctx);

@@ -42,6 +42,10 @@ int optimo_scene_json(void* h, char* out, int cap)
     return static_cast<int>(s.size());
 }
 int optimo_set_device(void* h, int device) { return guarded([&] { C(h)->SetDevice(device); }); }
+int optimo_set_devices(void* h, const int* devices, int n)
+{
+    return guarded([&] { C(h)->SetDevices(n > 0 && devices ? std::vector<int>(devices, devices + n) : std::vector<int>()); });
+}
 
 int optimo_min_frame(void* h) { return C(h)->min_frame_; }
 int optimo_max_frame(void* h) { return C(h)->max_frame_; }
@@ -215,19 +219,24 @@ int optimo_get_solve_trace(void* h, double* out)
     return guarded([&] { std::copy(C(h)->solve_trace_.begin(), C(h)->solve_trace_.end(), out); });
 }
 
+// optimo_cache_size takes ONE consistent copy of the cache (Core::GetOptimizationCache, thread-safe) and keeps it per calling
+// thread; optimo_get_cache then reads that copy. A UI thread polling during a solve therefore never sees arrays of two
+// different evaluations (or of two different windows) in one read-out.
+namespace { thread_local Core::OptimizationCache t_cache_snapshot; }
 int optimo_cache_size(void* h, int* n_samples, int* dof)
 {
     return guarded([&] {
-        const auto c = C(h)->GetOptimizationCache();
+        t_cache_snapshot = C(h)->GetOptimizationCache();
+        const auto& c = t_cache_snapshot;
         *n_samples = c.GetSize();
         *dof = c.q.empty() ? 0 : static_cast<int>(c.q[0].size());
     });
 }
-/// which: 0 time, 1 q, 2 q_dot, 3 q_ddot, 4 tau, 5 local_cost
+/// which: 0 time, 1 q, 2 q_dot, 3 q_ddot, 4 tau, 5 local_cost -- of the copy taken by this thread's last optimo_cache_size
 int optimo_get_cache(void* h, int which, double* out)
 {
     return guarded([&] {
-        const auto c = C(h)->GetOptimizationCache();
+        const auto& c = t_cache_snapshot;
         auto dump = [&](const std::vector<VecN>& a) { for (const VecN& r : a) { std::copy(r.begin(), r.end(), out); out += r.size(); } };
         switch (which) {
             case 0: std::copy(c.time_sequence.begin(), c.time_sequence.end(), out); break;
@@ -278,6 +287,12 @@ void* optimo_engine(void* h)
 {
     void* e = nullptr;
     guarded([&] { e = C(h)->Engine(); });
+    return e;
+}
+void* optimo_engine_multi(void* h)
+{
+    void* e = nullptr;
+    guarded([&] { e = C(h)->MultiEngine(); });
     return e;
 }
 /// Pushes window / weights / x_original into the engine (what every evaluation does first) and returns it.

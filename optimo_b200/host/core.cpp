@@ -133,6 +133,7 @@ Core::Core()
 
 Core::~Core()
 {
+    if (multi_) { omo_destroy_multi(multi_); engine_ = nullptr; }
     if (engine_) omo_destroy(engine_);
 }
 
@@ -349,15 +350,35 @@ void Core::Check(omo_status st, const char* what)
 
 void Core::InitializeDynamicsModel()
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    if (multi_) { omo_destroy_multi(multi_); multi_ = nullptr; engine_ = nullptr; }   // the multi engine owned engine_
     if (engine_) { omo_destroy(engine_); engine_ = nullptr; }
     ClearOptimizationCache();
     have_last_ = false;
+}
+
+void Core::SetDevices(const std::vector<int>& devices)
+{
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    if (devices == devices_) return;
+    devices_ = devices;
+    if (!devices_.empty()) device_ = devices_[0];
+    InitializeDynamicsModel();
+}
+
+omo_multi* Core::MultiEngine()
+{
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    if (devices_.size() < 2) return nullptr;
+    Engine();
+    return multi_;
 }
 
 /// Flattens the object graph into the tables of omo_scene_desc: what Core::InitializeDynamicsModel
 /// (core_rbdl.cpp:200-262) feeds to RBDL plus the channel / control-point layout of Object::GetDescriptor.
 omo_ctx* Core::Engine()
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     if (engine_) return engine_;
     const auto joints = object_->GetJoints();
     const auto iks = object_->GetIkHandlers();
@@ -401,6 +422,12 @@ omo_ctx* Core::Engine()
         probe_status_ = static_cast<int>(ps);
         return nullptr;
     }
+    if (devices_.size() >= 2) {
+        const omo_status st = omo_create_multi(&d, devices_.data(), static_cast<int>(devices_.size()), &multi_);
+        if (st != OMO_OK) { multi_ = nullptr; throw engine_error(std::string("omo_create_multi: ") + omo_multi_last_error(nullptr)); }
+        engine_ = omo_multi_ctx(multi_, 0);
+        return engine_;
+    }
     const omo_status st = omo_create(&d, device_, &engine_);
     if (st != OMO_OK) { engine_ = nullptr; throw engine_error(std::string("omo_create: ") + omo_last_error(nullptr)); }
     return engine_;
@@ -408,6 +435,7 @@ omo_ctx* Core::Engine()
 
 int Core::ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_prefix, std::string* log)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     omo_ctx* keep = engine_;
     engine_ = nullptr;
     probe_only_ = true; probe_fk_ = fk ? 1 : 0; probe_count_ = count ? 1 : 0; probe_prefix_ = dump_prefix;
@@ -438,23 +466,50 @@ void Core::SyncEngineState(const VecN& x_original)
     Check(omo_set_original(e, x_original.data(), static_cast<int>(x_original.size())), "omo_set_original");
 }
 
+/// The same snapshot pushed to every device of the multi engine (batches and gradients only).
+void Core::SyncMulti(double min_t, double max_t, const VecN& x_original)
+{
+    const VecN w = CalculateParameterWeights();
+    if (x_original.size() != w.size()) throw std::invalid_argument("x_original has the wrong length");
+    std::vector<omo_gauss> ks;
+    for (const GaussianKernel& k : kernels_) ks.push_back(omo_gauss{k.amp, k.mu, k.sigma});
+    auto check = [&](omo_status st, const char* what) { if (st != OMO_OK) throw engine_error(std::string(what) + ": " + omo_multi_last_error(multi_)); };
+    check(omo_multi_set_window(multi_, min_t, max_t, 0.20), "omo_multi_set_window");
+    check(omo_multi_set_weights(multi_, w.data(), static_cast<int>(w.size()), weight_trajectory_, ks.data(), static_cast<int>(ks.size()),
+                                object_->is_cyclic_ ? 1 : 0), "omo_multi_set_weights");
+    check(omo_multi_set_original(multi_, x_original.data(), static_cast<int>(x_original.size())), "omo_multi_set_original");
+}
+
 double Core::CalculateFullObjective(double min_t, double max_t, const VecN& x, const VecN& x_original)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     SyncEngine(min_t, max_t, x_original);
     if (x.size() != x_original.size()) throw std::invalid_argument("x has the wrong length");
     double f = 0.0;
     Check(omo_eval(engine_, x.data(), 1, &f, &last_terms_), "omo_eval");
-    object_->SetDescriptor(x);  // the reference leaves the object at x (core_rbdl.cpp:371)
-    {
-        std::lock_guard<std::mutex> g(optimization_cache_mutex_);
-        last_x_ = x; last_min_t_ = min_t; last_max_t_ = max_t; have_last_ = true; cache_stale_ = true;
-    }
+    NoteEvaluated(x, min_t, max_t);
     return f;
+}
+
+/// What every evaluation leaves behind: the object sits at x (core_opt.cpp:40 "modifies the object and does not restore it",
+/// core_rbdl.cpp:371) and the OptimizationCache belongs to x from now on.
+void Core::NoteEvaluated(const VecN& x, double min_t, double max_t)
+{
+    object_->SetDescriptor(x);
+    std::lock_guard<std::mutex> g(optimization_cache_mutex_);
+    last_x_ = x; last_min_t_ = min_t; last_max_t_ = max_t; have_last_ = true; cache_stale_ = true;
 }
 
 void Core::CalculateFullObjectiveBatch(double min_t, double max_t, const double* X, int B, const VecN& x_original, double* f_out,
                                        omo_terms* terms_out)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    Engine();
+    if (multi_) {
+        SyncMulti(min_t, max_t, x_original);
+        if (omo_multi_eval(multi_, X, B, f_out, terms_out) != OMO_OK) throw engine_error(std::string("omo_multi_eval: ") + omo_multi_last_error(multi_));
+        return;
+    }
     SyncEngine(min_t, max_t, x_original);
     Check(omo_eval(engine_, X, B, f_out, terms_out), "omo_eval");
 }
@@ -462,19 +517,29 @@ void Core::CalculateFullObjectiveBatch(double min_t, double max_t, const double*
 double Core::CalculateFullObjectiveAndGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
                                                const std::vector<int>& free_indices, double h, VecN* grad, VecN* f_plus_minus)
 {
-    SyncEngine(min_t, max_t, x_original);
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    Engine();
     if (x.size() != x_original.size()) throw std::invalid_argument("x has the wrong length");
     const int F = static_cast<int>(free_indices.size());
     grad->assign(F, 0.0);
     if (f_plus_minus) f_plus_minus->assign(2 * static_cast<size_t>(F), 0.0);
     double f0 = 0.0;
-    Check(omo_eval_grad(engine_, x.data(), free_indices.data(), F, h, &f0, grad->data(), f_plus_minus ? f_plus_minus->data() : nullptr),
-          "omo_eval_grad");
+    if (multi_) {
+        SyncMulti(min_t, max_t, x_original);
+        if (omo_multi_eval_grad(multi_, x.data(), free_indices.data(), F, h, &f0, grad->data(), f_plus_minus ? f_plus_minus->data() : nullptr) != OMO_OK)
+            throw engine_error(std::string("omo_multi_eval_grad: ") + omo_multi_last_error(multi_));
+    } else {
+        SyncEngine(min_t, max_t, x_original);
+        Check(omo_eval_grad(engine_, x.data(), free_indices.data(), F, h, &f0, grad->data(), f_plus_minus ? f_plus_minus->data() : nullptr),
+              "omo_eval_grad");
+    }
+    NoteEvaluated(x, min_t, max_t);
     return f0;
 }
 
 std::vector<double> Core::CalculatePositions(double min_t, double max_t, const VecN& x)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     SyncEngine(min_t, max_t, x_original_);
     std::vector<double> p(static_cast<size_t>(omo_num_samples(engine_)) * omo_dof(engine_));
     Check(omo_positions(engine_, x.data(), p.data()), "omo_positions");
@@ -485,6 +550,7 @@ std::vector<double> Core::CalculatePositions(double min_t, double max_t, const V
 
 void Core::CalculateTorquesBatch(const double* times, int M, double* tau, double* q, double* qd, double* qdd)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     const VecN x = object_->GetDescriptor();
     SyncEngineState(x_original_.size() == x.size() ? x_original_ : x);
     Check(omo_eval_states_at(engine_, x.data(), times, M, 0.20, q, qd, qdd, tau, nullptr, nullptr), "omo_eval_states_at");
@@ -499,6 +565,7 @@ VecN Core::CalculateTorques(double t)
 
 std::vector<double> Core::CalculateEulerAngles(const double* times, int M)
 {
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     const VecN x = object_->GetDescriptor();
     SyncEngineState(x_original_.size() == x.size() ? x_original_ : x);
     const size_t dof = 3 * object_->GetJoints().size();
@@ -523,6 +590,8 @@ void Core::UpdateMaximumTorqueAndCost()
 
 Core::OptimizationCache Core::GetOptimizationCache()
 {
+    // lock order: engine, then cache (CalculateFullObjective holds the engine and takes the cache mutex at its end)
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     std::lock_guard<std::mutex> g(optimization_cache_mutex_);
     if (cache_stale_ || optimization_cache_.time_sequence.empty()) {
         // The reference computes CalculateCost(min_frame-1, max_frame+1, 0.2) of the current object when no cache

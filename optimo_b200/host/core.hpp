@@ -103,8 +103,11 @@ public:
         std::vector<double> local_cost_sequence;
         int GetSize() const { return static_cast<int>(time_sequence.size()); }
     };
-    /// Thread-safe copy. The per-sample arrays of the last evaluated x are fetched from the GPU on demand
-    /// (the reference fills them on every evaluation, core_rbdl.cpp:341-343; the observable content is the same).
+    /// Thread-safe copy (the UI thread polls it at 30 Hz while the solver thread evaluates, mainwindow.cpp:228-235,
+    /// core.h:132-143). The per-sample arrays of the last evaluated x are fetched from the GPU on demand (the reference
+    /// fills them on every evaluation, core_rbdl.cpp:341-343; the observable content is the same). Like every method
+    /// that drives the engine it takes engine_mutex_ for the whole omo_* sequence: an omo_ctx serves one host thread
+    /// at a time (include/omo.h), so a cache / torque query waits for the evaluation in flight and vice versa.
     OptimizationCache GetOptimizationCache();
     void ClearOptimizationCache();
 
@@ -124,6 +127,12 @@ public:
     /// CUDA device the engine is created on (default 0, or $OPTIMO_DEVICE / $LOCAL_RANK).
     void SetDevice(int device);
     int GetDevice() const { return device_; }
+    /// Several GPUs of one box behind the SAME calls: batches are sharded over candidates and gradients
+    /// over their 2F+1 finite-difference columns by an omo_multi (include/omo.h); single evaluations run on the first
+    /// device. Results are bit-identical to the one-device engine. An empty / one-entry list goes back to SetDevice.
+    void SetDevices(const std::vector<int>& devices);
+    const std::vector<int>& GetDevices() const { return devices_; }
+    omo_multi* MultiEngine();   // nullptr unless SetDevices named >= 2 devices
     /// The engine behind the objective; created lazily (never before main), rebuilt when the scene changes.
     omo_ctx* Engine();
     /// Generates and NVRTC-compiles the scene-specialised objective kernel of the current scene on the host (no GPU
@@ -146,6 +155,8 @@ public:
 private:
     void SyncEngine(double min_t, double max_t, const VecN& x_original);
     void SyncEngineState(const VecN& x_original);   // weights + x_original, no window
+    void SyncMulti(double min_t, double max_t, const VecN& x_original);
+    void NoteEvaluated(const VecN& x, double min_t, double max_t);
     void ApplyJsonToScene(const std::string& json_text);   // core_io.cpp:228-250
     std::string FrameJson(int frame, const double* euler) const;
     std::vector<std::string> history_;              // core.h: std::list<std::string> history_
@@ -153,7 +164,11 @@ private:
 
     std::vector<GaussianKernel> kernels_;
     VecN x_original_;
-    omo_ctx* engine_ = nullptr;
+    omo_ctx* engine_ = nullptr;       // owned, or omo_multi_ctx(multi_, 0) when multi_ exists
+    omo_multi* multi_ = nullptr;
+    std::vector<int> devices_;
+    /// Serialises every omo_* sequence (SyncEngine .. last copy-out) between the solver thread and UI-side queries.
+    std::recursive_mutex engine_mutex_;
     bool probe_only_ = false;
     int probe_fk_ = 0, probe_count_ = 0, probe_status_ = 0;
     std::string probe_prefix_, probe_log_;

@@ -136,7 +136,8 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     constexpr int dim = 5;
     constexpr double epsilon = 1e-06;
 
-    VecN x_initial = object_->GetDescriptor();
+    VecN x_initial;
+    { std::lock_guard<std::recursive_mutex> eg(engine_mutex_); x_initial = object_->GetDescriptor(); }   // UI-side queries read the object too
     const int n = static_cast<int>(x_initial.size()) / dim;
     const VecN x_original = RetrieveOriginalParameters();
     if (x_initial.size() != x_original.size()) throw std::logic_error("x_original does not match the descriptor");
@@ -178,7 +179,10 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     last_solve_status_ = "";
     solve_trace_.clear();
     solve_trace_dim_ = static_cast<int>(M);
-    if (M == 0) { object_->SetDescriptor(x_initial); last_solve_status_ = "no free dofs"; return; }
+    if (M == 0) {
+        std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+        object_->SetDescriptor(x_initial); last_solve_status_ = "no free dofs"; return;
+    }
 
     // nloptutil::solve (nlopt-util.hpp:44-195)
     NloptApi& api = nlopt_api();
@@ -235,7 +239,7 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     std::cout << "Function evals : " << numevals << std::endl;
     std::cout << "--------------------" << std::endl;
 
-    object_->SetDescriptor(rev(x_star));
+    { std::lock_guard<std::recursive_mutex> eg(engine_mutex_); object_->SetDescriptor(rev(x_star)); }
 }
 
 }  // namespace optimo

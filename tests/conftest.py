@@ -76,3 +76,20 @@ def configure(obj, case, is_oracle):
 def rel_err(a, b):
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
     return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-300))
+
+
+def elem_err(a, b, rtol):
+    """Element-wise deviation in units of the allowed one: max_i |a_i - b_i| / (rtol * |b_i| + 1e-12 * max|b|).
+    <= 1 passes. Unlike rel_err (one ratio for the whole array) a small entry cannot hide behind a large one: an entry of
+    1e-6 of the largest that is 100 % wrong scores ~1e6. The absolute floor (1e-12 of the largest entry) is what SURVEY.md
+    App. B prescribes for the O(1e-16) stencil residues of constant channels, which the pruned walk returns as exact zeros."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    floor = 1e-12 * max(float(np.max(np.abs(b))) if b.size else 0.0, 1e-300)
+    return float(np.max(np.abs(a - b) / (rtol * np.abs(b) + floor))) if b.size else 0.0
+
+
+def gradient_bound(g_ref, f0, h, tol=1e-9):
+    """Allowed |g - g_ref|_inf. SURVEY.md section 8(d): 1e-9 * max(|g|_inf, 1). The central difference divides two values that
+    each carry the summation-order difference between the tile-tree reduction and the reference's serial loop (<= 2e-14
+    relative, N_s terms) by 2h, so that share is added explicitly (DESIGN.md section 2 states the same bound)."""
+    return tol * max(float(np.max(np.abs(g_ref))) if g_ref.size else 0.0, 1.0) + 2e-14 * abs(f0) / (2.0 * h)
