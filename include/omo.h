@@ -134,6 +134,11 @@ omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx
  * device. Asynchronous on the ctx stream unless `sync` != 0. */
 omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync);
 
+/* Host candidates in (X[B][D], pinned for a truly asynchronous copy; chunked and overlapped with the kernels exactly like omo_eval),
+ * values left in DEVICE memory: d_f_out[B], optionally d_terms_out[3B]. What a rank of a multi-process job calls before it
+ * gathers its shard with NCCL. Asynchronous on the ctx stream unless `sync` != 0. */
+omo_status omo_eval_host_in(omo_ctx* ctx, const double* X, int B, double* d_f_out, double* d_terms_out, int sync);
+
 /* One evaluation that also fills the OptimizationCache of the reference (core.h:120-152): each of
  * q, qd, qdd, tau is [N_s * dof] sample-major, local_cost is [N_s]; any of them may be NULL. */
 omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd,
@@ -239,6 +244,9 @@ omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* lau
  * <dump_prefix>.cu / .cubin when dump_prefix is not NULL. */
 omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int log_cap);
 omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const char* dump_prefix, char* log, int log_cap);
+/* JSON list of the specialised instances this context has built: form (unrolled / loop), registers, shared memory, build time
+ * (NVRTC, or the load from the on-disk cubin cache: $OMO_JIT_CACHE_DIR, else <dir of libomo.so>/jit_cache; OMO_JIT_CACHE=0 disables it). */
+omo_status omo_jit_describe(omo_ctx* ctx, char* out, int cap);
 
 /* Device self-test of the hand-scheduled FP64 division used by the curve solver (omo_kernels.cuh: div_rn_fast;
  * it replaces the `f / f'` of SolveCubic, OptiMo/curve.cpp:50): q_fast[i] = the branch-free sequence, ok[i] = its

@@ -133,6 +133,7 @@ _OMO_SIG = {
     "omo_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
     "omo_eval_free": (ci, [_vp, _dp, _ip, ci, _dp, ci, _dp, _dp]),
     "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
+    "omo_eval_host_in": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
     "omo_eval_grad_columns": (ci, [_vp, _dp, _ip, ci, cd, ci, ci, _vp, ci]),
     "omo_grad_from_columns": (ci, [_dp, ci, cd, _dp, _dp]),
@@ -150,6 +151,7 @@ _OMO_SIG = {
     "omo_kernel_timing": (ci, [_vp, ci, _dp, _ip]),
     "omo_measure_dfma_peak": (ci, [_vp, _dp]),
     "omo_jit_info": (ci, [_vp, C.POINTER(_ull), cs, ci]),
+    "omo_jit_describe": (ci, [_vp, C.c_char_p, ci]),
     "omo_selftest_division": (ci, [_vp, _dp, _dp, ci, _dp, _dp, _ip]),
     "omo_grad_sparsity": (ci, [_vp, C.POINTER(_ull)]),
     "omo_graph_replays": (_ull, [_vp]),
@@ -270,6 +272,10 @@ class Engine:
     def eval_device(self, dX, B, dF, dTerms=None, sync=True):
         self._ck(_omo.omo_eval_device(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device")
 
+    def eval_host_in(self, x_ptr, B, dF, dTerms=None, sync=False):
+        """omo_eval_host_in: host (pinned) candidates in, values left on the device."""
+        self._ck(_omo.omo_eval_host_in(self.h, x_ptr, B, dF, dTerms, int(sync)), "omo_eval_host_in")
+
     def eval_grad(self, x, free_idx, h=1e-4):
         x, xp = _d(x)
         idx, ip = _i(free_idx)
@@ -344,6 +350,12 @@ class Engine:
         self._ck(_omo.omo_jit_info(self.h, out, buf, len(buf)), "omo_jit_info")
         return {"launches": int(out[0]), "instances": int(out[1]), "max_registers": int(out[2]), "compile_ms": int(out[3]),
                 "log": buf.value.decode(errors="replace")}
+
+    def jit_describe(self):
+        """The specialised kernel instances this engine built (form, registers, shared memory, build time, cache hit)."""
+        buf = C.create_string_buffer(1 << 14)
+        self._ck(_omo.omo_jit_describe(self.h, buf, len(buf)), "omo_jit_describe")
+        return json.loads(buf.value.decode() or "[]")
 
     def selftest_division(self, num, den):
         """(q_fast, q_ref, ok) of the curve solver's hand-scheduled division on the device (include/omo.h)."""

@@ -842,8 +842,12 @@ omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, 
 
 // Host rows of width W (W = D: whole candidates into d_X; W = F with `expand`: free entries into d_Xfree, expanded on the device)
 // copied and evaluated chunk by chunk; f (and the terms) copied back; synchronised on return.
-omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, double* d_stage, bool expand, int F, double* f_out, omo_terms* terms_out)
+// d_f_dst != nullptr: the values stay on the device (d_f_dst[B], optionally d_terms_dst[3B]) and nothing is copied back or waited for.
+omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, double* d_stage, bool expand, int F, double* f_out, omo_terms* terms_out,
+                               double* d_f_dst = nullptr, double* d_terms_dst = nullptr)
 {
+    double* const d_f = d_f_dst ? d_f_dst : ctx->d_f;
+    double* const d_terms = d_f_dst ? d_terms_dst : (terms_out ? ctx->d_terms : nullptr);
     omo_status st;
     // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
     // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
@@ -860,7 +864,7 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
             OMO_CUDA(cudaGetLastError());
             ctx->launches += 1;
         }
-        return eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, ctx->d_f + b0, terms_out ? ctx->d_terms + (size_t)3 * b0 : nullptr);
+        return eval_device_impl(ctx, ctx->d_X + (size_t)b0 * ctx->D, nb, d_f + b0, d_terms ? d_terms + (size_t)3 * b0 : nullptr);
     };
     if (n_chunks == 1) {
         OMO_CUDA(cudaMemcpyAsync(d_stage, X, bytes, cudaMemcpyHostToDevice, ctx->stream));
@@ -899,6 +903,7 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
             if ((st = evaluate(b0, nb)) != OMO_OK) return st;
         }
     }
+    if (d_f_dst) return OMO_OK;
     OMO_CUDA(cudaMemcpyAsync(f_out, ctx->d_f, (size_t)B * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (terms_out) OMO_CUDA(cudaMemcpyAsync(terms_out, ctx->d_terms, (size_t)B * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1133,6 +1138,19 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
         ctx->sg_pending = key;
     }
     return eval_host_pipelined(ctx, X, B, ctx->D, ctx->d_X, false, 0, f_out, terms_out);
+}
+
+omo_status omo_eval_host_in(omo_ctx* ctx, const double* X, int B, double* d_f_out, double* d_terms_out, int sync)
+{
+    DeviceLock device_lock(ctx);
+    if (!ctx || (!X && ctx->D > 0) || !d_f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (B == 0) return OMO_OK;
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
+    if ((st = eval_host_pipelined(ctx, X, B, ctx->D, ctx->d_X, false, 0, nullptr, nullptr, d_f_out, d_terms_out)) != OMO_OK) return st;
+    if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
 }
 
 omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx, int F, const double* Xfree, int B, double* f_out, omo_terms* terms_out)
@@ -1493,7 +1511,14 @@ omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const c
         omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk != 0 || ik, ik, count != 0);
         std::vector<char> cubin;
         std::string clog;
-        const bool ok = omo_jit::compile(spec.source, cubin, clog, spec.sub);
+        // the same key acquire_jit uses: a probe on the build machine pre-populates the on-disk cubin cache of the run machine
+        const uint64_t key = omo_jit::fnv1a(spec.source + "#sub" + std::to_string(spec.sub)) ^ omo_jit::headers_hash();
+        bool ok = omo_jit::disk_cache_load(key, cubin);
+        if (ok) clog = "(cubin taken from the on-disk cache)";
+        else {
+            ok = omo_jit::compile(spec.source, cubin, clog, spec.sub);
+            if (ok) omo_jit::disk_cache_store(key, cubin);
+        }
         if (dump_prefix) {
             if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cu").c_str(), "w")) { std::fputs(spec.source.c_str(), fh); std::fclose(fh); }
             if (ok) if (FILE* fh = std::fopen((std::string(dump_prefix) + ".cubin").c_str(), "wb")) { std::fwrite(cubin.data(), 1, cubin.size(), fh); std::fclose(fh); }
@@ -1519,6 +1544,27 @@ omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int l
             if (k.ok) { out4[1] += 1; out4[2] = std::max<unsigned long long>(out4[2], (unsigned long long)k.regs); out4[3] += (unsigned long long)k.compile_ms; }
     }
     if (log && log_cap > 0) { std::strncpy(log, ctx->jit_log.c_str(), (size_t)log_cap - 1); log[log_cap - 1] = 0; }
+    return OMO_OK;
+}
+
+omo_status omo_jit_describe(omo_ctx* ctx, char* out, int cap)
+{
+    if (!ctx || !out || cap <= 0) return OMO_BAD_ARG;
+    std::string t = "[";
+    bool first = true;
+    for (int i = 0; i < 8; ++i) {
+        const omo_ctx::JitKernel& k = ctx->jit[i];
+        if (!k.ok) continue;
+        char buf[320];
+        std::snprintf(buf, sizeof(buf), "%s{\"fk\": %s, \"ik\": %s, \"count\": %s, \"form\": \"%s\", \"registers\": %d, \"smem_bytes\": %zu, "
+                      "\"items_per_block\": %d, \"build_ms\": %.1f, \"from_disk_cache\": %s}",
+                      first ? "" : ", ", (i & 1) ? "true" : "false", (i & 2) ? "true" : "false", (i & 4) ? "true" : "false",
+                      k.loop_form ? "loop" : "unrolled", k.regs, k.smem, k.sub, k.compile_ms, k.from_disk ? "true" : "false");
+        t += buf;
+        first = false;
+    }
+    t += "]";
+    std::strncpy(out, t.c_str(), (size_t)cap - 1); out[cap - 1] = 0;
     return OMO_OK;
 }
 
