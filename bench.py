@@ -269,11 +269,15 @@ class Gpu:
         return ms, wall, kt, launches
 
 
+_KEEP = []   # engines outlive every torch tensor that was used on their streams (torch records an event on that stream when it frees one)
+
+
 def build(name, device):
     from optimo_b200.core import Core
     scene = make_scene(name)
     desc, B = WORKLOADS[name]
     core = Core(scene, device=device)
+    _KEEP.append(core)
     if name == "grad_conductor":
         core.set_kernels(CONDUCTOR_KERNELS)
     core.UpdateGlobalWeight(W_TRAJ.get(name, 0.0))
@@ -452,6 +456,7 @@ def measure_solve(G, dfma_peak):
     from optimo_b200.core import Core
     scene = load_scene("fox-tail")
     c = Core(scene, device=G.local)
+    _KEEP.append(c)
     c.select_items(["tail_root", "tail_center"])
     x_init = c.GetDescriptor()
     c.UpdateOriginalParameters(x_init)
@@ -728,6 +733,7 @@ def run_multi_gpu(G, args):
     if rank == 0 and not args.no_single_process:
         try:
             cm = Core(W.scene, devices=list(range(world)))
+            _KEEP.append(cm)
             Fm = eng.pinned_array((B,)); Xm = eng.pinned_array((B, W.D)); Xm[:] = X_all
             m = None
             res = {}
@@ -754,9 +760,9 @@ def run_multi_gpu(G, args):
                 t_g = (time.perf_counter() - t0) / 50
                 assert gm[0] == grad_box["f0"] and np.array_equal(gm[1], grad_box["g"]), "multi-device gradient differs"
                 res[label] = {"batch_ms": t_b * 1e3, "batch_value": B * W.N_s / t_b, "gradient_us": t_g * 1e6, "bit_identical": True}
+            del m
             single = {"api": "omo_create_multi / omo_multi_eval / omo_multi_eval_grad (one host thread, one worker per device; host wall clock, pinned X in, f out)",
                       "devices": world, "gather": res}
-            del cm
         except Exception as e:   # noqa: BLE001
             single = {"error": str(e)[:300]}
     if G.cpu_group is not None:
@@ -811,6 +817,8 @@ def _reserve_stdout():
 
 def main():
     global print
+    import faulthandler
+    faulthandler.enable()
     out = _reserve_stdout()
     _print = print
 
