@@ -620,6 +620,7 @@ def run_multi_gpu(G, args):
     B = W.B
     X_all = syn.perturbed_candidates(W.x0, B, first=0)          # the ONE batch; every rank can build it, each uses its slice only
     b0, nb = shard_range(B, rank, world)
+    eng.set_batch_hint(B)    # the kernel the whole batch gets, whatever a rank's share
     pad = (B + world - 1) // world
     dXs = torch.empty((max(nb, 1), W.D), dtype=torch.float64, device="cuda")
     dFs = torch.zeros(pad, dtype=torch.float64, device="cuda")

@@ -106,6 +106,12 @@ omo_status omo_set_weights(omo_ctx* ctx, const double* w_param, int D, double w_
 /* x_original (core.h:237-243): uploads it and rebuilds p_original (N_s x 3J) on the device. */
 omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D);
 
+/* Which kernel evaluates a batch (scene-specialised or table-driven; they agree to ~1e-13, not bit for bit) depends on the size
+ * of the launch. A context that evaluates a SLICE of a larger batch (one device of omo_multi, one rank of a multi-process job)
+ * names the whole batch here, so that the choice -- and with it every bit of the result -- does not depend on how the batch was
+ * split. 0 = no hint. */
+omo_status omo_set_batch_hint(omo_ctx* ctx, int total_candidates);
+
 /* ---- queries ---------------------------------------------------------------------------------------- */
 int omo_num_samples(const omo_ctx* ctx);  /* N_s */
 int omo_descriptor_size(const omo_ctx* ctx); /* D */
@@ -241,7 +247,8 @@ omo_status omo_kernel_timing(omo_ctx* ctx, int reset, double* total_ms, int* lau
  * omo_jit_info: out4[0] launches that went through a specialised kernel, [1] instances compiled, [2] their largest
  * register count, [3] total compile time in ms; log = why specialisation was not possible, if it was not.
  * omo_jit_probe (host only, needs no GPU): generates and compiles the specialised kernel of `scene`; writes
- * <dump_prefix>.cu / .cubin when dump_prefix is not NULL. */
+ * <dump_prefix>.cu / .cubin when dump_prefix is not NULL. count: bit 0 = the work-counting instance, bit 1 = the
+ * self-preparing instance (single candidates / small gradients in one launch). The cubin also lands in the on-disk cache. */
 omo_status omo_jit_info(omo_ctx* ctx, unsigned long long* out4, char* log, int log_cap);
 omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const char* dump_prefix, char* log, int log_cap);
 /* JSON list of the specialised instances this context has built: form (unrolled / loop), registers, shared memory, build time

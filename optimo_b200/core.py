@@ -133,6 +133,7 @@ _OMO_SIG = {
     "omo_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
     "omo_eval_free": (ci, [_vp, _dp, _ip, ci, _dp, ci, _dp, _dp]),
     "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
+    "omo_set_batch_hint": (ci, [_vp, ci]),
     "omo_eval_host_in": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
     "omo_eval_grad_columns": (ci, [_vp, _dp, _ip, ci, cd, ci, ci, _vp, ci]),
@@ -271,6 +272,10 @@ class Engine:
 
     def eval_device(self, dX, B, dF, dTerms=None, sync=True):
         self._ck(_omo.omo_eval_device(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device")
+
+    def set_batch_hint(self, total):
+        """This engine evaluates slices of a batch of `total` candidates (kernel choice by the whole batch; 0 = off)."""
+        self._ck(_omo.omo_set_batch_hint(self.h, int(total)), "omo_set_batch_hint")
 
     def eval_host_in(self, x_ptr, B, dF, dTerms=None, sync=False):
         """omo_eval_host_in: host (pinned) candidates in, values left on the device."""
@@ -708,10 +713,11 @@ class Core:
         self._ck(_core.optimo_perform_optimization_gradient(self.h, int(explicit_termination), algorithm.encode(), C.byref(v), C.byref(n)))
         return v.value, n.value
 
-    def probe_specialised_kernel(self, fk=False, count=False, dump_prefix=None):
-        """Host-only: generates and NVRTC-compiles the scene-specialised kernel; returns (ok, log)."""
+    def probe_specialised_kernel(self, fk=False, count=False, dump_prefix=None, self_preparing=False):
+        """Host-only: generates and NVRTC-compiles the scene-specialised kernel (self_preparing: the one-launch instance for
+        single candidates and small gradients); returns (ok, log)."""
         buf = C.create_string_buffer(1 << 16)
-        rc = _core.optimo_probe_specialised_kernel(self.h, int(fk), int(count), dump_prefix.encode() if dump_prefix else None, buf, len(buf))
+        rc = _core.optimo_probe_specialised_kernel(self.h, int(fk), int(bool(count)) | (2 if self_preparing else 0), dump_prefix.encode() if dump_prefix else None, buf, len(buf))
         return rc == 0, buf.value.decode(errors="replace")
 
     def record_solve_trace(self, on=True):

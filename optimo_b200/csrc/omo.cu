@@ -67,9 +67,10 @@ struct omo_ctx {
         unsigned long long uploaded_version = 0;
         double compile_ms = 0.0;
     };
-    JitKernel jit[8];
+    JitKernel jit[16];   // index: fk | ik << 1 | count << 2 | self << 3
     int jit_mode = -1;            // -1: auto (large launches), 0: never, 1: always (OMO_JIT)
     bool prefer_jit = false;      // this launch takes the specialised kernel whatever its size (gradient columns: never by shard size)
+    int batch_hint = 0;           // omo_set_batch_hint: candidates of the whole batch this context evaluates a slice of
     std::string jit_log;
     unsigned long long jit_launches = 0;
 
@@ -129,6 +130,15 @@ struct omo_ctx {
     unsigned long long sg_kernels = 0, sg_replays = 0;
     double* h_single = nullptr;                 // pinned: x [D], then f, C, D_param, D_traj
     double* d_single = nullptr;                 // device: f, C, D_param, D_traj of the single candidate (one copy-out)
+
+    // self-preparing launches (Walker SELF): one launch per single candidate / small gradient, x as a kernel parameter
+    int self_mode = -1;                         // OMO_SELF=0 switches it off
+    double* d_self_dparam = nullptr; int self_rows_cap = 0;
+    unsigned* d_self_counter = nullptr;
+    double* h_self_out = nullptr;               // mapped pinned host memory the kernel writes f into: [max(4, self_out_cap)]
+    double* d_self_out = nullptr;               // its device alias
+    int self_out_cap = 0;
+    unsigned long long self_launches = 0;
 
     // counters / timing
     unsigned long long* d_counters = nullptr;
@@ -500,17 +510,17 @@ int jit_mode(omo_ctx* ctx)
 
 // Compiles (once) and returns the specialised kernel of an instance, or nullptr when it cannot be had -- the caller
 // then launches the table-driven kernel, which is the same CUDA code driven by tables.
-omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count)
+omo_ctx::JitKernel* acquire_jit(omo_ctx* ctx, bool fk, bool ik, bool count, bool self = false)
 {
-    omo_ctx::JitKernel& k = ctx->jit[(fk ? 1 : 0) | (ik ? 2 : 0) | (count ? 4 : 0)];
+    omo_ctx::JitKernel& k = ctx->jit[(fk ? 1 : 0) | (ik ? 2 : 0) | (count ? 4 : 0) | (self ? 8 : 0)];
     if (k.tried) return k.ok ? &k : nullptr;
     k.tried = true;
     omo_jit::Api& a = omo_jit::api();
     if (!a.have_nvrtc() || !a.have_driver()) { ctx->jit_log = "JIT unavailable:" + a.error; return nullptr; }
     const auto t0 = std::chrono::steady_clock::now();
-    omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk, ik, count);
+    omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk, ik, count, self ? ctx->n_cp : 0);
     if (const char* dump = std::getenv("OMO_JIT_DUMP")) {
-        if (FILE* fh = std::fopen((std::string(dump) + (fk ? "_fk" : "") + (ik ? "_ik" : "") + (count ? "_count" : "") + ".cu").c_str(), "w")) {
+        if (FILE* fh = std::fopen((std::string(dump) + (fk ? "_fk" : "") + (ik ? "_ik" : "") + (count ? "_count" : "") + (self ? "_self" : "") + ".cu").c_str(), "w")) {
             std::fputs(spec.source.c_str(), fh); std::fclose(fh);
         }
     }
@@ -599,7 +609,8 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     // large launches run the scene-specialised kernel (auto: >= 64 K sample-evals; OMO_JIT=1 always, OMO_JIT=0 never)
     const int mode = jit_mode(ctx);
     // (sparse column launches always do: a gradient's columns must not switch kernels with the size of a rank's shard)
-    if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || ctx->prefer_jit || (long long)P.n_items * plan.t_out >= 65536)) {
+    const long long sized_as = std::max<long long>(P.n_items, (long long)ctx->batch_hint * plan.n_tiles);
+    if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || ctx->prefer_jit || sized_as * plan.t_out >= 65536)) {
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
             if (d_item_map) return OMO_OK;
@@ -795,7 +806,7 @@ bool affected_tiles(omo_ctx* ctx, const double* x, const int* free_idx, int F, i
                 // samples with t_lo <= t <= t_hi, one sample of slack each side, then the stencil's two
                 const int s_lo = (int)(std::lower_bound(tg.begin(), tg.end(), t_lo) - tg.begin()) - 3;
                 const int s_hi = (int)(std::upper_bound(tg.begin(), tg.end(), t_hi) - tg.begin()) - 1 + 3;
-                if (s_hi < 0 || s_lo > N - 1) { lo = 1; hi = 0; }
+                if (s_hi < 0 || s_lo > N - 1) { lo = 0; hi = 0; }   // out of reach of the window: one tile anyway (it equals the base point's), so that every row has a block that books its D_param
                 else { lo = std::max(s_lo, 0) / T_out; hi = std::min(std::min(s_hi, N - 1) / T_out, n_tiles - 1); }
             }
         }
@@ -826,6 +837,79 @@ std::vector<unsigned long long> single_key(const omo_ctx* ctx)
     for (long long v : ints) k.push_back((unsigned long long)v);
     k.push_back(bits(ctx->dt)); k.push_back(bits(ctx->w_traj)); k.push_back(ctx->scene_version);
     return k;
+}
+
+// ---- self-preparing launches ------------------------------------------------------------------------------------------------
+constexpr int kSelfMaxCp = 192;     // control points whose prepared form + segment records fit beside the walk's shared memory
+constexpr int kSelfMaxRows = 2048;
+
+bool self_usable(omo_ctx* ctx)
+{
+    if (ctx->self_mode < 0) { const char* e = std::getenv("OMO_SELF"); ctx->self_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
+    return ctx->self_mode == 1 && jit_mode(ctx) != 0 && !ctx->timing && !ctx->counting && ctx->n_cp >= 1 && ctx->n_cp <= kSelfMaxCp;
+}
+
+omo_status ensure_self_buffers(omo_ctx* ctx, int rows)
+{
+    omo_status st;
+    if (!ctx->d_self_counter) {
+        if ((st = dev_alloc(ctx, &ctx->d_self_counter, 1)) != OMO_OK) return st;
+        OMO_CUDA(cudaMemsetAsync(ctx->d_self_counter, 0, sizeof(unsigned), ctx->stream));
+    }
+    if (rows > ctx->self_rows_cap) {
+        const int cap = std::max(rows, 256);
+        if ((st = dev_alloc(ctx, &ctx->d_self_dparam, (size_t)cap)) != OMO_OK) return st;
+        ctx->self_rows_cap = cap;
+    }
+    if (std::max(rows, 4) > ctx->self_out_cap) {
+        const int cap = std::max(rows, 256);
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->h_self_out) { cudaFreeHost(ctx->h_self_out); ctx->h_self_out = nullptr; }
+        OMO_CUDA(cudaHostAlloc((void**)&ctx->h_self_out, (size_t)cap * sizeof(double), cudaHostAllocMapped));
+        OMO_CUDA(cudaHostGetDevicePointer((void**)&ctx->d_self_out, ctx->h_self_out, 0));
+        ctx->self_out_cap = cap;
+    }
+    return OMO_OK;
+}
+
+// One launch: rows of the finite-difference list (or the one candidate x) x their tiles. `out` must be device-visible.
+// item_map / lo / hi as in the sparse column path (null: every tile of every row); base_row = -1 without a base row.
+omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_row, const int* d_item_map, int n_items, const int* d_lo, const int* d_hi,
+                       const int* d_free, double h, int col_begin, double* out, bool* launched)
+{
+    *launched = false;
+    const bool ik = ctx->n_ik > 0;
+    const bool fk = (ctx->w_traj != 0.0) || ik;
+    omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, false, true);
+    if (!k) return OMO_OK;    // the caller takes the general path
+    omo_status st;
+    if ((st = ensure_capacity(ctx, rows)) != OMO_OK) return st;
+    if ((st = ensure_self_buffers(ctx, rows)) != OMO_OK) return st;
+    OmoEvalParams P;
+    fill_params(ctx, P);
+    P.counters = nullptr;
+    P.p_orig = (ctx->w_traj != 0.0) ? ctx->d_p_orig : nullptr;
+    const LaunchPlan plan = make_plan(ctx, rows, fk, ik, false);
+    P.n_tiles = plan.n_tiles; P.T_out = plan.t_out; P.smem_stride = 0; P.n_smem_slots = plan.smem_slots;
+    P.item_map = d_item_map;
+    P.n_items = d_item_map ? n_items : rows * plan.n_tiles;
+    P.self_free = d_free; P.self_lo = d_lo; P.self_hi = d_hi;
+    P.self_cp_of_pos = ctx->d_cp_of_pos; P.self_first_of_pos = ctx->d_first_of_pos; P.self_last_of_pos = ctx->d_last_of_pos; P.self_next_same = ctx->d_next_same;
+    P.self_x0 = ctx->d_x0; P.self_wparam = ctx->d_wparam;
+    P.self_dparam = ctx->d_self_dparam; P.self_out = out; P.self_counter = ctx->d_self_counter;
+    P.self_h = h; P.self_col_begin = col_begin; P.self_rows = rows; P.self_base_row = base_row; P.self_cyclic = ctx->cyclic; P.self_D = ctx->D;
+    omo_jit::Api& a = omo_jit::api();
+    if (k->uploaded_version != ctx->scene_version) {
+        OMO_CUDA(cudaMemcpyAsync(reinterpret_cast<void*>(k->d_scene), &ctx->hs, sizeof(OmoDevScene), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        k->uploaded_version = ctx->scene_version;
+    }
+    void* args[] = {&P, const_cast<double*>(x_host)};   // second parameter: the descriptor itself, D doubles by value
+    const int rc = a.cuLaunchKernel(k->fn, (unsigned)P.n_items, 1, 1, kBlockThreads, 1, 1, (unsigned)k->smem, reinterpret_cast<omo_jit::CUstream>(ctx->stream), args, nullptr);
+    if (rc != 0) return fail(ctx, OMO_CUDA_ERROR, "cuLaunchKernel(self-preparing omo_jit_kernel) failed with CUresult " + std::to_string(rc));
+    ctx->launches += 1; ctx->jit_launches += 1; ctx->self_launches += 1;
+    *launched = true;
+    return OMO_OK;
 }
 
 omo_status eval_device_impl(omo_ctx* ctx, const double* dX, int B, double* d_f, double* d_terms)
@@ -963,6 +1047,9 @@ void omo_destroy(omo_ctx* ctx)
     if (ctx->d_Xfree) cudaFree(ctx->d_Xfree);
     if (ctx->d_inv_free) cudaFree(ctx->d_inv_free);
     if (ctx->d_single) cudaFree(ctx->d_single);
+    if (ctx->d_self_dparam) cudaFree(ctx->d_self_dparam);
+    if (ctx->d_self_counter) cudaFree(ctx->d_self_counter);
+    if (ctx->h_self_out) cudaFreeHost(ctx->h_self_out);
     for (auto& k : ctx->jit) if (k.mod) omo_jit::api().cuModuleUnload(k.mod);
     for (auto& pr : ctx->timed) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
     for (auto& e : ctx->chunk_ev) if (e) cudaEventDestroy(e);
@@ -1026,6 +1113,13 @@ omo_status omo_set_original(omo_ctx* ctx, const double* x_original, int D)
     if (st != OMO_OK) return st;
     ctx->have_original = true;
     ctx->p_orig_dirty = true;
+    return OMO_OK;
+}
+
+omo_status omo_set_batch_hint(omo_ctx* ctx, int total_candidates)
+{
+    if (!ctx || total_candidates < 0) return OMO_BAD_ARG;
+    ctx->batch_hint = total_candidates;
     return OMO_OK;
 }
 
@@ -1095,6 +1189,19 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
     const size_t bytes = (size_t)B * ctx->D * sizeof(double);
     if (ctx->graph_mode < 0) { const char* e = std::getenv("OMO_GRAPH"); ctx->graph_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
+    if (B == 1 && self_usable(ctx)) {
+        // one launch: x travels as a kernel parameter, the kernel prepares, evaluates, reduces and writes (f, C, D_param, D_traj)
+        // into mapped host memory
+        if ((st = ensure_self_buffers(ctx, 1)) != OMO_OK) return st;
+        bool launched = false;
+        if ((st = launch_self(ctx, X, 1, -1, nullptr, 0, nullptr, nullptr, nullptr, 0.0, 0, ctx->d_self_out, &launched)) != OMO_OK) return st;
+        if (launched) {
+            OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+            *f_out = ctx->h_self_out[0];
+            if (terms_out) { terms_out->C = ctx->h_self_out[1]; terms_out->D_param = ctx->h_self_out[2]; terms_out->D_traj = ctx->h_self_out[3]; }
+            return OMO_OK;
+        }
+    }
     if (B == 1 && ctx->graph_mode == 1 && !ctx->timing) {
         // The solver's callback: one candidate per call, thousands of calls. The first call with a given state runs the plain
         // path below (it finishes every lazy allocation / module load), the second captures, the rest replay.
@@ -1321,7 +1428,6 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     if ((st = ensure_capacity(ctx, col_count)) != OMO_OK) return st;
     if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
     if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; ctx->free_uploaded.clear(); }
-    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     if (F > 0 && (ctx->free_uploaded.size() != (size_t)F || !std::equal(ctx->free_uploaded.begin(), ctx->free_uploaded.end(), free_idx))) {
         ctx->free_uploaded.assign(free_idx, free_idx + F);
         OMO_CUDA(cudaMemcpyAsync(ctx->d_free, ctx->free_uploaded.data(), (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
@@ -1333,15 +1439,7 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
     const bool sparse = std::getenv("OMO_GRAD_DENSE") == nullptr && affected_tiles(ctx, x, free_idx, F, col_begin, col_count);
     const int rows = sparse ? col_count + 1 : col_count;
     if (sparse && (st = ensure_capacity(ctx, rows)) != OMO_OK) return st;
-    omo::perturb_kernel<<<rows, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
-    OMO_CUDA(cudaGetLastError());
-    ctx->launches += 1;
-    if (!sparse) {
-        ctx->prefer_jit = true;    // same kernel as the sparse columns of the other shards
-        st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr);
-        ctx->prefer_jit = false;
-        if (st != OMO_OK) return st;
-    } else {
+    auto upload_items = [&]() -> omo_status {
         if (ctx->h_items.size() > ctx->items_cap) {
             if ((st = dev_alloc(ctx, &ctx->d_items, ctx->h_items.size())) != OMO_OK) return st;
             ctx->items_cap = ctx->h_items.size(); ctx->sp_uploaded = false;
@@ -1357,6 +1455,31 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
             OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // the host vectors are pageable
             ctx->sp_uploaded = true;
         }
+        return OMO_OK;
+    };
+    if (sparse && rows <= kSelfMaxRows && self_usable(ctx)) {
+        // small gradients: ONE launch -- x as a kernel parameter, every block builds its column's control points itself, the last
+        // block adds the tile partials (same numbers in the same order as the launches below: bit-identical)
+        if ((st = upload_items()) != OMO_OK) return st;
+        bool launched = false;
+        if ((st = launch_self(ctx, x, rows, col_count, ctx->d_items, (int)ctx->h_items.size(), ctx->d_lohi, ctx->d_lohi + col_count, ctx->d_free, h, col_begin,
+                              d_f_cols, &launched)) != OMO_OK) return st;
+        if (launched) {
+            if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+            return OMO_OK;
+        }
+    }
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    omo::perturb_kernel<<<rows, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    if (!sparse) {
+        ctx->prefer_jit = true;    // same kernel as the sparse columns of the other shards
+        st = eval_device_impl(ctx, ctx->d_X, col_count, d_f_cols, nullptr);
+        ctx->prefer_jit = false;
+        if (st != OMO_OK) return st;
+    } else {
+        if ((st = upload_items()) != OMO_OK) return st;
         if ((st = run_prepare(ctx, ctx->d_X, rows)) != OMO_OK) return st;
         OmoEvalParams P;
         fill_params(ctx, P);
@@ -1388,10 +1511,18 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     omo_status st = ensure_ready(ctx);
     if (st != OMO_OK) return st;
     if ((st = ensure_capacity(ctx, P + 1)) != OMO_OK) return st;   // + the base row of the sparse evaluation: d_f must not move below
-    if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
     ctx->h_cols.resize(P);
+    if (P + 1 <= kSelfMaxRows && self_usable(ctx)) {
+        // the column values are written straight into mapped host memory (by the self-preparing kernel, or by finish_sparse_kernel
+        // if that launch is not to be had): no copy-out
+        if ((st = ensure_self_buffers(ctx, P)) != OMO_OK) return st;
+        if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_self_out, 1)) != OMO_OK) return st;
+        std::copy(ctx->h_self_out, ctx->h_self_out + P, ctx->h_cols.begin());
+    } else {
+    if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_f, 0)) != OMO_OK) return st;
     OMO_CUDA(cudaMemcpyAsync(ctx->h_cols.data(), ctx->d_f, (size_t)P * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
     if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
     return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
 }
@@ -1508,7 +1639,8 @@ omo_status omo_jit_probe(const omo_scene_desc* scene, int fk, int count, const c
     std::string msg;
     if (st == OMO_OK) {
         const bool ik = ctx->n_ik > 0;
-        omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk != 0 || ik, ik, count != 0);
+        const bool self = (count & 2) != 0;   // `count` bit 1: the self-preparing instance
+        omo_jit::KernelSpec spec = omo_jit::generate(ctx->hs, fk != 0 || ik, ik, (count & 1) != 0 && !self, self ? ctx->n_cp : 0);
         std::vector<char> cubin;
         std::string clog;
         // the same key acquire_jit uses: a probe on the build machine pre-populates the on-disk cubin cache of the run machine
@@ -1552,13 +1684,13 @@ omo_status omo_jit_describe(omo_ctx* ctx, char* out, int cap)
     if (!ctx || !out || cap <= 0) return OMO_BAD_ARG;
     std::string t = "[";
     bool first = true;
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 16; ++i) {
         const omo_ctx::JitKernel& k = ctx->jit[i];
         if (!k.ok) continue;
-        char buf[320];
-        std::snprintf(buf, sizeof(buf), "%s{\"fk\": %s, \"ik\": %s, \"count\": %s, \"form\": \"%s\", \"registers\": %d, \"smem_bytes\": %zu, "
+        char buf[360];
+        std::snprintf(buf, sizeof(buf), "%s{\"fk\": %s, \"ik\": %s, \"count\": %s, \"self_preparing\": %s, \"form\": \"%s\", \"registers\": %d, \"smem_bytes\": %zu, "
                       "\"items_per_block\": %d, \"build_ms\": %.1f, \"from_disk_cache\": %s}",
-                      first ? "" : ", ", (i & 1) ? "true" : "false", (i & 2) ? "true" : "false", (i & 4) ? "true" : "false",
+                      first ? "" : ", ", (i & 1) ? "true" : "false", (i & 2) ? "true" : "false", (i & 4) ? "true" : "false", (i & 8) ? "true" : "false",
                       k.loop_form ? "loop" : "unrolled", k.regs, k.smem, k.sub, k.compile_ms, k.from_disk ? "true" : "false");
         t += buf;
         first = false;

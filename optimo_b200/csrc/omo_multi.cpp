@@ -334,7 +334,10 @@ omo_status omo_multi_eval(omo_multi* m, const double* X, int B, double* f_out, o
         int b0 = 0, nb = 0;
         omo_shard_range(B, i, m->n, &b0, &nb);
         if (nb == 0) return OMO_OK;
-        return omo_eval(m->ctx[i], X + (size_t)b0 * D, nb, f_out + b0, terms_out ? terms_out + b0 : nullptr);
+        omo_set_batch_hint(m->ctx[i], B);   // the kernel the whole batch would get, whatever this device's share
+        const omo_status s = omo_eval(m->ctx[i], X + (size_t)b0 * D, nb, f_out + b0, terms_out ? terms_out + b0 : nullptr);
+        omo_set_batch_hint(m->ctx[i], 0);
+        return s;
     });
 }
 
@@ -346,7 +349,10 @@ omo_status omo_multi_eval_free(omo_multi* m, const double* x_base, const int* fr
         int b0 = 0, nb = 0;
         omo_shard_range(B, i, m->n, &b0, &nb);
         if (nb == 0) return OMO_OK;
-        return omo_eval_free(m->ctx[i], x_base, free_idx, F, Xfree + (size_t)b0 * F, nb, f_out + b0, terms_out ? terms_out + b0 : nullptr);
+        omo_set_batch_hint(m->ctx[i], B);
+        const omo_status s = omo_eval_free(m->ctx[i], x_base, free_idx, F, Xfree + (size_t)b0 * F, nb, f_out + b0, terms_out ? terms_out + b0 : nullptr);
+        omo_set_batch_hint(m->ctx[i], 0);
+        return s;
     });
 }
 

@@ -119,6 +119,22 @@ struct OmoEvalParams {
     int triplet;
     int n_smem_slots;  // deep-tree instance of the table-driven kernel: stack slots held in shared memory, the rest per thread
     double* o_root;
+    // ---- self-preparing instances (Walker SELF; single candidates and small finite-difference gradients) --------------------
+    // One launch does what the batch path spreads over perturb_kernel -> prepare_kernel -> objective -> finish_kernel and two
+    // copies: the base descriptor x arrives as a KERNEL PARAMETER (constant bank), every block prepares its row's control
+    // points in shared memory itself (row r = x, or x with entry self_free[(col-1)>>1] moved by +-h for column col =
+    // self_col_begin + r > 0), the block that finishes last adds the tile partials in order (finish_sparse_kernel's rule:
+    // tiles outside [lo, hi] of a row come from self_base_row) and writes f straight into mapped host memory.
+    const int* self_free;       // [F] free descriptor indices (gradient rows), null for plain candidates
+    const int* self_lo;         // [rows] first / last tile evaluated for the row (null: every tile)
+    const int* self_hi;
+    const int *self_cp_of_pos, *self_first_of_pos, *self_last_of_pos, *self_next_same;   // prepare tables (see OmoPrepParams)
+    const double *self_x0, *self_wparam;   // [D]
+    double* self_dparam;        // [rows] scratch
+    double* self_out;           // [rows] f (rows == 1: f, C, D_param, D_traj), device-visible (mapped host or device memory)
+    unsigned* self_counter;     // blocks finished; the last one resets it
+    double self_h;
+    int self_col_begin, self_rows, self_base_row, self_cyclic, self_D;
 };
 
 #endif

@@ -36,7 +36,11 @@ namespace omo {
 // DEEP (table-driven kernel only): trees whose stack does not fit shared memory (a 128-joint chain parks 127 bodies). Slots
 // below `nsm` live in shared memory as usual, slot nsm + r is the per-thread rs[r] (run-time indexed = local memory, which
 // the driver provisions per RESIDENT thread -- the pooling a global scratch buffer would have to re-invent).
-template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0, bool CPT = false, bool DEEP = false>
+// SELF (scene-specialised kernels only; needs SEGG > 0, OMO_SUB == 1): the block prepares its row's control points itself, in
+// shared memory, from the base descriptor handed over as a kernel parameter; the last block to finish reduces the tile
+// partials and writes f (OmoEvalParams::self_*). One launch per call: what a single candidate (every BOBYQA callback,
+// core_opt.cpp:145) and the 109-157-column gradients of the shipped scenes need, where launches and copies, not FLOPs, set the time.
+template <bool FK, bool IK, bool OUT, bool COUNT, int NREG = 0, int SEGG = 0, bool CPT = false, bool DEEP = false, bool SELF = false>
 struct Walker {
     static constexpr int NT = OMO_NT;
     static constexpr int TREE = OUT ? 0 : 1;   // 0: every body, 1: candidate-independent subtrees pruned
@@ -73,6 +77,9 @@ struct Walker {
     double* wsb;                      //           staging buffers [buf][SEGG][OMO_SEGW][OMO_SEGD]
     int* wbase;                       //           [n_keyed] chain position of each keyed channel's first staged record
     const unsigned short* __restrict__ tsg;   //   this (candidate, tile)'s row of the tile table
+    const double* xs;                 // SELF: the base descriptor (kernel parameter, constant bank)
+    double* seg_sm;                   //       this row's segment records [n_cp + OMO_SEGW][OMO_SEGD] in shared memory
+    int cand_, tile_;
 
     __device__ __forceinline__ Walker(const OmoEvalParams& P_) : P(P_) {}
 
@@ -120,18 +127,31 @@ struct Walker {
         if (P.item_map) item = __ldg(P.item_map + item);   // sparse launches (finite-difference columns): listed (candidate, tile) pairs only
         const int cand = item / P.n_tiles;
         const int tile = item - cand * P.n_tiles;
+        cand_ = cand; tile_ = tile;
         const int ex_rows = S.n_ex_rows + (IK ? 6 : 0);
         ex = smem;
         double* stk0 = smem + ex_rows * NT;
         stk = stk0 + tid;
         N = P.N_s;
         tile_end = min(N, (tile + 1) * P.T_out);
-        pc = P.prep + (size_t)cand * 6 * P.n_cp;
-        sorted = (__ldg(P.flags + cand) & 1u) != 0u;
         dof = (size_t)3 * S.J;
         n_bez = n_newton = n_iksolve = n_ikiter = 0u;
         xbuf = 0;
-        if (SEGG > 0) {
+        if (SELF) {
+            seg0 = nullptr; sgc = nullptr; tsg = nullptr; wsb = nullptr;
+            double* tail = stk0 + (size_t)n_smem_slots * ((CPT ? 1 : OMO_SLOT) * NT);
+            const int wb_doubles = ((S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double);
+            wbase = reinterpret_cast<int*>(tail);
+            double* prep_sm = tail + wb_doubles;
+            seg_sm = prep_sm + 6 * P.n_cp;
+            pc = prep_sm;
+            self_prepare(prep_sm, tile);
+        } else {
+        pc = P.prep + (size_t)cand * 6 * P.n_cp;
+        sorted = (__ldg(P.flags + cand) & 1u) != 0u;
+        }
+        if (SELF) {
+        } else if (SEGG > 0) {
             // staged curves: wbase[] and the staging buffers sit behind the stack -- or, when the only curve group opens
             // the walk (stage_in_stack), in the stack area itself, which no body has touched yet
             seg0 = nullptr;
@@ -194,7 +214,7 @@ struct Walker {
             double e[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k)
-                e[k] = (S.dyn[0] >> k & 1) ? eval_channel(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], t, sorted, n_bez, n_newton) : S.chan_const[k];
+                e[k] = (S.dyn[0] >> k & 1) ? eval_channel<!SELF>(pc, P.n_cp, S.chan_pos[k], S.chan_n[k], t, sorted, n_bez, n_newton) : S.chan_const[k];
             if (OUT && owned && P.o_root) { P.o_root[s * 3] = e[0]; P.o_root[s * 3 + 1] = e[1]; P.o_root[s * 3 + 2] = e[2]; }
             double sx, cx, sy, cy, sz, cz;
             sincos_angle(e[0], &sx, &cx); sincos_angle(e[1], &sy, &cy); sincos_angle(e[2], &sz, &cz);
@@ -209,6 +229,108 @@ struct Walker {
             }
             if (OUT && owned && P.o_p) { P.o_p[s * dof] = W[0]; P.o_p[s * dof + 1] = W[1]; P.o_p[s * dof + 2] = W[2]; }
         }
+    }
+
+    // ---- SELF: Object::SetDescriptor + MakeMotionCyclic + handle values + segment records + D_param of this block's row, in
+    // shared memory (the arithmetic of perturb_kernel and prepare_kernel, operation for operation) ----------------------------
+    __device__ __forceinline__ void self_prepare(double* __restrict__ prep_sm, const int tile)
+    {
+        const OmoDevScene& S = c_scene;
+        const int n_cp = P.n_cp, D = P.self_D;
+        __shared__ double red[NT / 32];
+        __shared__ int unsorted;
+        int kpert = -1;
+        double step = 0.0;
+        if (P.self_free && cand_ != P.self_base_row) {   // column col of the finite-difference list: col 0 = x, 2k+1 / 2k+2 = x +- h e_k
+            const int col = P.self_col_begin + cand_;
+            if (col > 0) { kpert = __ldg(P.self_free + ((col - 1) >> 1)); step = ((col - 1) & 1) ? -P.self_h : P.self_h; }
+        }
+        auto X = [&](const int i) { double v = xs[i]; if (i == kpert) v = v + step; return v; };
+        if (tid == 0) unsorted = 0;
+        for (int pos = tid; pos < n_cp; pos += NT) {
+            const int cp = __ldg(P.self_cp_of_pos + pos);
+            const double t0 = X(5 * cp), v = X(5 * cp + 1), tb = X(5 * cp + 3), tf = X(5 * cp + 4);
+            double th = X(5 * cp + 2);
+            if (P.self_cyclic) {
+                const int fi = __ldg(P.self_first_of_pos + pos), la = __ldg(P.self_last_of_pos + pos);
+                if (cp == fi || cp == la) th = __dmul_rn(0.5, __dadd_rn(X(5 * fi + 2), X(5 * la + 2)));
+            }
+            const double tn = tan(th);
+            prep_sm[pos] = t0; prep_sm[n_cp + pos] = v; prep_sm[2 * n_cp + pos] = __dadd_rn(t0, tf); prep_sm[3 * n_cp + pos] = __dadd_rn(t0, tb);
+            prep_sm[4 * n_cp + pos] = __dadd_rn(v, __dmul_rn(tf, tn)); prep_sm[5 * n_cp + pos] = __dadd_rn(v, __dmul_rn(tb, tn));
+        }
+        // D_param (core_rbdl.cpp:385), in prepare_kernel's order: strided partial sums, shuffle tree, the four warps in turn
+        double acc = 0.0;
+        for (int k = tid; k < D; k += NT) {
+            const double d = X(k) - __ldg(P.self_x0 + k);
+            acc = __fma_rn(__dmul_rn(d, __ldg(P.self_wparam + k)), d, acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if ((tid & 31) == 0) red[tid >> 5] = acc;
+        __syncthreads();
+        if (tid == 0) {
+            double sum = 0.0;
+            for (int w = 0; w < NT / 32; ++w) sum += red[w];
+            const int lo_tile = P.self_lo ? __ldg(P.self_lo + cand_) : 0;
+            if (tile == lo_tile) P.self_dparam[cand_] = sum;
+        }
+        for (int pos = tid; pos < n_cp; pos += NT) {
+            if (__ldg(P.self_next_same + pos) && !(prep_sm[pos] <= prep_sm[pos + 1])) unsorted = 1;
+            if (pos >= 1 && __ldg(P.self_next_same + pos - 1)) {
+                const double p0 = prep_sm[pos - 1], p1 = prep_sm[2 * n_cp + pos - 1], p2 = prep_sm[3 * n_cp + pos], p3 = prep_sm[pos];
+                const double a = __dadd_rn(__dsub_rn(__dadd_rn(-p0, __dmul_rn(3.0, p1)), __dmul_rn(3.0, p2)), p3);
+                double* __restrict__ r = seg_sm + (size_t)pos * OMO_SEGD;
+                r[0] = p0; r[1] = p3; r[2] = a;
+                r[3] = __dmul_rn(3.0, __dadd_rn(__dsub_rn(p0, __dmul_rn(2.0, p1)), p2));
+                r[4] = __dadd_rn(__dmul_rn(-3.0, p0), __dmul_rn(3.0, p1));
+                r[5] = __dmul_rn(3.0, a);
+                r[6] = prep_sm[n_cp + pos - 1]; r[7] = prep_sm[4 * n_cp + pos - 1]; r[8] = prep_sm[5 * n_cp + pos]; r[9] = prep_sm[n_cp + pos];
+            }
+        }
+        // first staged record of every keyed channel for this tile (prepare_kernel's tile table + stage_base)
+        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2, 0), N - 1));
+        for (int i = tid; i < S.n_keyed; i += NT) {
+            const int ch = S.grp_list[i];
+            const double* __restrict__ T = prep_sm + S.chan_pos[ch];
+            const int n = S.chan_n[ch];
+            int lo = 0, hi = n;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (T[mid] <= t_first) lo = mid + 1; else hi = mid;
+            }
+            wbase[i] = (n >= 2) ? min(max(lo, 1), n - 1) : 1;
+        }
+        __syncthreads();
+        sorted = unsorted == 0;
+    }
+
+    // SELF: the block that finishes last adds the tile partials of every row in tile order (finish_kernel / finish_sparse_kernel)
+    __device__ __forceinline__ void self_finish()
+    {
+        __shared__ int last_block;
+        if (tid == 0) {
+            __threadfence();
+            const unsigned ticket = atomicAdd(P.self_counter, 1u);
+            last_block = (ticket == (unsigned)P.n_items - 1u) ? 1 : 0;
+        }
+        __syncthreads();
+        if (!last_block) return;
+        __threadfence();
+        const int rows_out = P.self_base_row >= 0 ? P.self_rows - 1 : P.self_rows;
+        for (int r = tid; r < rows_out; r += NT) {
+            const int l = P.self_lo ? __ldg(P.self_lo + r) : 0, h = P.self_hi ? __ldg(P.self_hi + r) : P.n_tiles - 1;
+            double C = 0.0, Dt = 0.0;
+            for (int tl = 0; tl < P.n_tiles; ++tl) {
+                const int row = (tl >= l && tl <= h) ? r : P.self_base_row;
+                C += __ldcg(P.partial + ((size_t)row * P.n_tiles + tl) * 2);
+                Dt += __ldcg(P.partial + ((size_t)row * P.n_tiles + tl) * 2 + 1);
+            }
+            const double Dp = __ldcg(P.self_dparam + r);
+            P.self_out[r] = C + Dp + Dt;
+            if (P.self_rows == 1) { P.self_out[1] = C; P.self_out[2] = Dp; P.self_out[3] = Dt; }
+        }
+        if (tid == 0) *P.self_counter = 0u;
     }
 
     // ---- stack traffic ---------------------------------------------------------------------------------------------
@@ -292,7 +414,7 @@ struct Walker {
         double tw[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k)
-            tw[k] = (S.ik_chan_n[h][k] > 0) ? eval_channel(pc, P.n_cp, S.ik_chan_pos[h][k], S.ik_chan_n[h][k], t, sorted, n_bez, n_newton)
+            tw[k] = (S.ik_chan_n[h][k] > 0) ? eval_channel<!SELF>(pc, P.n_cp, S.ik_chan_pos[h][k], S.ik_chan_n[h][k], t, sorted, n_bez, n_newton)
                                             : S.ik_chan_const[h][k];
         double Lp[9], tp[3];
 #pragma unroll
@@ -340,7 +462,7 @@ struct Walker {
     template <bool FIRST = false>
     __device__ __forceinline__ void stage_issue(const int buf, const int g0, const int nch)
     {
-        if (SEGG == 0 || !sorted) return;
+        if (SEGG == 0 || SELF || !sorted) return;
         const OmoDevScene& S = c_scene;
         constexpr int U = OMO_SEGD / 2;   // 16-byte units per record
         const int items = nch * OMO_SEGW * U;
@@ -357,7 +479,7 @@ struct Walker {
     }
     __device__ __forceinline__ void stage_wait()
     {
-        if (SEGG > 0) asm volatile("cp.async.wait_all;" ::: "memory");
+        if (SEGG > 0 && !SELF) asm volatile("cp.async.wait_all;" ::: "memory");
     }
 
     // K (<= 3) keyed joint channels (entries i0.. of grp_list, rows lc0.. of staging buffer buf) sampled in lockstep from
@@ -372,8 +494,8 @@ struct Walker {
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 unsigned eb = 0, en = 0;
-                val[k] = COUNT ? eval_channel(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false, eb, en)
-                               : eval_channel_slow(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false);
+                val[k] = COUNT ? eval_channel<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false, eb, en)
+                               : eval_channel_slow<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false);
                 if (COUNT && owned) { n_bez += eb; n_newton += en; }
             }
         } else {
@@ -381,7 +503,8 @@ struct Walker {
             int nn[K], base[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                sk[k] = wsb + (size_t)((buf * SEGG + lc0 + k) * OMO_SEGW) * OMO_SEGD;
+                sk[k] = SELF ? seg_sm + (size_t)(S.chan_pos[ch[k]] + wbase[i0 + k]) * OMO_SEGD
+                             : wsb + (size_t)((buf * SEGG + lc0 + k) * OMO_SEGW) * OMO_SEGD;
                 nn[k] = S.chan_n[ch[k]];
                 base[k] = wbase[i0 + k];
             }
@@ -391,8 +514,8 @@ struct Walker {
 #pragma unroll
                 for (int k = 0; k < K; ++k)
                     if (fb >> k & 1u)
-                        val[k] = COUNT ? eval_channel(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true, eb, en)
-                                       : eval_channel_slow(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true);
+                        val[k] = COUNT ? eval_channel<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true, eb, en)
+                                       : eval_channel_slow<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true);
             }
             if (COUNT && owned) { n_bez += eb; n_newton += en; }
         }
@@ -647,6 +770,7 @@ struct Walker {
             P.partial[(size_t)item * 2] = C;
             P.partial[(size_t)item * 2 + 1] = D;
         }
+        if (SELF) self_finish();
         if (COUNT && P.counters) {
             unsigned cb = n_bez, cn = n_newton, ci = n_iksolve, cj = n_ikiter;
 #pragma unroll

@@ -200,7 +200,7 @@ int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump
     int status = 0;
     const int rc = guarded([&] {
         std::string l;
-        status = C(h)->ProbeSpecialisedKernel(fk != 0, count != 0, dump_prefix ? dump_prefix : "", &l);
+        status = C(h)->ProbeSpecialisedKernel(fk != 0, count, dump_prefix ? dump_prefix : "", &l);
         if (log && cap > 0) { std::strncpy(log, l.c_str(), static_cast<size_t>(cap) - 1); log[cap - 1] = 0; }
     });
     return rc != 0 ? rc : (status == 0 ? 0 : 1);

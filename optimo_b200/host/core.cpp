@@ -433,12 +433,12 @@ omo_ctx* Core::Engine()
     return engine_;
 }
 
-int Core::ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_prefix, std::string* log)
+int Core::ProbeSpecialisedKernel(bool fk, int flags, const std::string& dump_prefix, std::string* log)
 {
     std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
     omo_ctx* keep = engine_;
     engine_ = nullptr;
-    probe_only_ = true; probe_fk_ = fk ? 1 : 0; probe_count_ = count ? 1 : 0; probe_prefix_ = dump_prefix;
+    probe_only_ = true; probe_fk_ = fk ? 1 : 0; probe_count_ = flags; probe_prefix_ = dump_prefix;
     try { Engine(); } catch (...) { probe_only_ = false; engine_ = keep; throw; }
     probe_only_ = false;
     engine_ = keep;

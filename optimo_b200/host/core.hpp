@@ -137,7 +137,7 @@ public:
     omo_ctx* Engine();
     /// Generates and NVRTC-compiles the scene-specialised objective kernel of the current scene on the host (no GPU
     /// needed); returns the omo_status, `log` gets the placement summary + compiler log. See omo_jit_probe.
-    int ProbeSpecialisedKernel(bool fk, bool count, const std::string& dump_prefix, std::string* log);
+    int ProbeSpecialisedKernel(bool fk, int flags, const std::string& dump_prefix, std::string* log);   // flags: omo_jit_probe's `count`
     /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
     void InitializeDynamicsModel();
 
