@@ -846,7 +846,7 @@ constexpr int kSelfMaxRows = 2048;
 bool self_usable(omo_ctx* ctx)
 {
     if (ctx->self_mode < 0) { const char* e = std::getenv("OMO_SELF"); ctx->self_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
-    return ctx->self_mode == 1 && jit_mode(ctx) != 0 && !ctx->timing && !ctx->counting && ctx->n_cp >= 1 && ctx->n_cp <= kSelfMaxCp;
+    return ctx->self_mode == 1 && jit_mode(ctx) != 0 && !ctx->counting && ctx->n_cp >= 1 && ctx->n_cp <= kSelfMaxCp;
 }
 
 omo_status ensure_self_buffers(omo_ctx* ctx, int rows)
@@ -904,9 +904,15 @@ omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_ro
         OMO_CUDA(cudaStreamSynchronize(ctx->stream));
         k->uploaded_version = ctx->scene_version;
     }
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->timing) {
+        OMO_CUDA(cudaEventCreate(&e0)); OMO_CUDA(cudaEventCreate(&e1));
+        OMO_CUDA(cudaEventRecord(e0, ctx->stream));
+    }
     void* args[] = {&P, const_cast<double*>(x_host)};   // second parameter: the descriptor itself, D doubles by value
     const int rc = a.cuLaunchKernel(k->fn, (unsigned)P.n_items, 1, 1, kBlockThreads, 1, 1, (unsigned)k->smem, reinterpret_cast<omo_jit::CUstream>(ctx->stream), args, nullptr);
     if (rc != 0) return fail(ctx, OMO_CUDA_ERROR, "cuLaunchKernel(self-preparing omo_jit_kernel) failed with CUresult " + std::to_string(rc));
+    if (e0) { OMO_CUDA(cudaEventRecord(e1, ctx->stream)); ctx->timed.emplace_back(e0, e1); }
     ctx->launches += 1; ctx->jit_launches += 1; ctx->self_launches += 1;
     *launched = true;
     return OMO_OK;
@@ -1457,7 +1463,8 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
         }
         return OMO_OK;
     };
-    if (sparse && rows <= kSelfMaxRows && self_usable(ctx)) {
+    // (every block prepares its row's n_cp control points itself: worth it while that stays small beside the blocks' own work)
+    if (sparse && rows <= kSelfMaxRows && (long long)ctx->h_items.size() * ctx->n_cp <= 60000 && self_usable(ctx)) {
         // small gradients: ONE launch -- x as a kernel parameter, every block builds its column's control points itself, the last
         // block adds the tile partials (same numbers in the same order as the launches below: bit-identical)
         if ((st = upload_items()) != OMO_OK) return st;

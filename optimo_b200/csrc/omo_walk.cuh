@@ -80,6 +80,8 @@ struct Walker {
     const double* xs;                 // SELF: the base descriptor (kernel parameter, constant bank)
     double* seg_sm;                   //       this row's segment records [n_cp + OMO_SEGW][OMO_SEGD] in shared memory
     int cand_, tile_;
+    double* self_red;                 //       D_param's per-warp partial sums (static shared memory), added up in finish()
+    bool self_books_dparam;
 
     __device__ __forceinline__ Walker(const OmoEvalParams& P_) : P(P_) {}
 
@@ -145,6 +147,8 @@ struct Walker {
             double* prep_sm = tail + wb_doubles;
             seg_sm = prep_sm + 6 * P.n_cp;
             pc = prep_sm;
+            __shared__ double self_red_store[NT / 32];
+            self_red = self_red_store;
             self_prepare(prep_sm, tile);
         } else {
         pc = P.prep + (size_t)cand * 6 * P.n_cp;
@@ -235,9 +239,11 @@ struct Walker {
     // shared memory (the arithmetic of perturb_kernel and prepare_kernel, operation for operation) ----------------------------
     __device__ __forceinline__ void self_prepare(double* __restrict__ prep_sm, const int tile)
     {
+        // Latency is all that matters here (one wave of blocks, one warp per scheduler): every thread works from the descriptor in
+        // the constant bank alone -- its own control point AND the one before it, so that the segment record needs no neighbour's
+        // result -- and the block meets at ONE barrier. D_param's partial sums wait in shared memory until finish().
         const OmoDevScene& S = c_scene;
         const int n_cp = P.n_cp, D = P.self_D;
-        __shared__ double red[NT / 32];
         __shared__ int unsorted;
         int kpert = -1;
         double step = 0.0;
@@ -246,8 +252,8 @@ struct Walker {
             if (col > 0) { kpert = __ldg(P.self_free + ((col - 1) >> 1)); step = ((col - 1) & 1) ? -P.self_h : P.self_h; }
         }
         auto X = [&](const int i) { double v = xs[i]; if (i == kpert) v = v + step; return v; };
-        if (tid == 0) unsorted = 0;
-        for (int pos = tid; pos < n_cp; pos += NT) {
+        // prepared point (t, v, t + t_f, t + t_b, v + t_f tan(theta), v + t_b tan(theta)) of chain position `pos`
+        auto point = [&](const int pos, double (&o)[6]) {
             const int cp = __ldg(P.self_cp_of_pos + pos);
             const double t0 = X(5 * cp), v = X(5 * cp + 1), tb = X(5 * cp + 3), tf = X(5 * cp + 4);
             double th = X(5 * cp + 2);
@@ -256,51 +262,60 @@ struct Walker {
                 if (cp == fi || cp == la) th = __dmul_rn(0.5, __dadd_rn(X(5 * fi + 2), X(5 * la + 2)));
             }
             const double tn = tan(th);
-            prep_sm[pos] = t0; prep_sm[n_cp + pos] = v; prep_sm[2 * n_cp + pos] = __dadd_rn(t0, tf); prep_sm[3 * n_cp + pos] = __dadd_rn(t0, tb);
-            prep_sm[4 * n_cp + pos] = __dadd_rn(v, __dmul_rn(tf, tn)); prep_sm[5 * n_cp + pos] = __dadd_rn(v, __dmul_rn(tb, tn));
-        }
-        // D_param (core_rbdl.cpp:385), in prepare_kernel's order: strided partial sums, shuffle tree, the four warps in turn
+            o[0] = t0; o[1] = v; o[2] = __dadd_rn(t0, tf); o[3] = __dadd_rn(t0, tb);
+            o[4] = __dadd_rn(v, __dmul_rn(tf, tn)); o[5] = __dadd_rn(v, __dmul_rn(tb, tn));
+        };
+        if (tid == 0) unsorted = 0;
+        // the tile's first sample time and D_param's operands: issued before anything waits on them
+        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2, 0), N - 1));
+        const int lo_tile = P.self_lo ? __ldg(P.self_lo + cand_) : 0;
         double acc = 0.0;
-        for (int k = tid; k < D; k += NT) {
-            const double d = X(k) - __ldg(P.self_x0 + k);
-            acc = __fma_rn(__dmul_rn(d, __ldg(P.self_wparam + k)), d, acc);
+        if (tile == lo_tile) {   // D_param (core_rbdl.cpp:385), in prepare_kernel's order: strided partial sums, shuffle tree, the four warps in turn
+            for (int k = tid; k < D; k += NT) {
+                const double d = X(k) - __ldg(P.self_x0 + k);
+                acc = __fma_rn(__dmul_rn(d, __ldg(P.self_wparam + k)), d, acc);
+            }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-        if ((tid & 31) == 0) red[tid >> 5] = acc;
-        __syncthreads();
-        if (tid == 0) {
-            double sum = 0.0;
-            for (int w = 0; w < NT / 32; ++w) sum += red[w];
-            const int lo_tile = P.self_lo ? __ldg(P.self_lo + cand_) : 0;
-            if (tile == lo_tile) P.self_dparam[cand_] = sum;
-        }
+        bool bad = false;
         for (int pos = tid; pos < n_cp; pos += NT) {
-            if (__ldg(P.self_next_same + pos) && !(prep_sm[pos] <= prep_sm[pos + 1])) unsorted = 1;
+            double cur[6];
+            point(pos, cur);
+#pragma unroll
+            for (int k = 0; k < 6; ++k) prep_sm[k * n_cp + pos] = cur[k];
+            if (__ldg(P.self_next_same + pos) && !(cur[0] <= X(5 * __ldg(P.self_cp_of_pos + pos + 1)))) bad = true;
             if (pos >= 1 && __ldg(P.self_next_same + pos - 1)) {
-                const double p0 = prep_sm[pos - 1], p1 = prep_sm[2 * n_cp + pos - 1], p2 = prep_sm[3 * n_cp + pos], p3 = prep_sm[pos];
+                double prv[6];
+                point(pos - 1, prv);
+                const double p0 = prv[0], p1 = prv[2], p2 = cur[3], p3 = cur[0];
                 const double a = __dadd_rn(__dsub_rn(__dadd_rn(-p0, __dmul_rn(3.0, p1)), __dmul_rn(3.0, p2)), p3);
                 double* __restrict__ r = seg_sm + (size_t)pos * OMO_SEGD;
                 r[0] = p0; r[1] = p3; r[2] = a;
                 r[3] = __dmul_rn(3.0, __dadd_rn(__dsub_rn(p0, __dmul_rn(2.0, p1)), p2));
                 r[4] = __dadd_rn(__dmul_rn(-3.0, p0), __dmul_rn(3.0, p1));
                 r[5] = __dmul_rn(3.0, a);
-                r[6] = prep_sm[n_cp + pos - 1]; r[7] = prep_sm[4 * n_cp + pos - 1]; r[8] = prep_sm[5 * n_cp + pos]; r[9] = prep_sm[n_cp + pos];
+                r[6] = prv[1]; r[7] = prv[4]; r[8] = cur[5]; r[9] = cur[1];
             }
         }
-        // first staged record of every keyed channel for this tile (prepare_kernel's tile table + stage_base)
-        const double t_first = __ldg(P.tgrid + min(max(tile * P.T_out - 2, 0), N - 1));
-        for (int i = tid; i < S.n_keyed; i += NT) {
+        if (bad) unsorted = 1;
+        // first staged record of every keyed channel for this tile (prepare_kernel's tile table + stage_base), searched on the
+        // key times of the descriptor itself; the last warps take it, the first ones are busy with the points
+        for (int i = NT - 1 - tid; i < S.n_keyed; i += NT) {
             const int ch = S.grp_list[i];
-            const double* __restrict__ T = prep_sm + S.chan_pos[ch];
+            const int* __restrict__ cpl = P.self_cp_of_pos + S.chan_pos[ch];
             const int n = S.chan_n[ch];
             int lo = 0, hi = n;
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
-                if (T[mid] <= t_first) lo = mid + 1; else hi = mid;
+                if (X(5 * __ldg(cpl + mid)) <= t_first) lo = mid + 1; else hi = mid;
             }
             wbase[i] = (n >= 2) ? min(max(lo, 1), n - 1) : 1;
         }
+        if (tile == lo_tile) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+            if ((tid & 31) == 0) self_red[tid >> 5] = acc;
+        }
+        self_books_dparam = tile == lo_tile;
         __syncthreads();
         sorted = unsorted == 0;
     }
@@ -310,6 +325,11 @@ struct Walker {
     {
         __shared__ int last_block;
         if (tid == 0) {
+            if (self_books_dparam) {
+                double sum = 0.0;
+                for (int w = 0; w < NT / 32; ++w) sum += self_red[w];
+                P.self_dparam[cand_] = sum;
+            }
             __threadfence();
             const unsigned ticket = atomicAdd(P.self_counter, 1u);
             last_block = (ticket == (unsigned)P.n_items - 1u) ? 1 : 0;
