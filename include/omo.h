@@ -40,7 +40,8 @@ typedef enum omo_status {
     OMO_CUDA_ERROR = 2,  /* any CUDA runtime failure, including "no device" */
     OMO_NCCL_ERROR = 3,
     OMO_OOM = 4,
-    OMO_NOT_READY = 5    /* window / weights / original parameters not set yet */
+    OMO_NOT_READY = 5,   /* window / weights / original parameters not set yet */
+    OMO_UNSUPPORTED = 6  /* the request is outside what this entry point covers (omo_eval_grad_analytic: IK scenes, unsorted keys) */
 } omo_status;
 
 typedef struct omo_ctx omo_ctx;
@@ -168,6 +169,17 @@ omo_status omo_eval_states_at(omo_ctx* ctx, const double* x, const double* times
  * evaluated as ONE batch of 2F+1 columns built on the device from x. f0_out, fpm_out ([F][2] = f+, f-) optional. */
 omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int F, double h, double* f0_out,
                          double* grad_out, double* fpm_out);
+
+/* NEW, next row N4: the ANALYTIC gradient of f on the free parameters -- forward-mode derivatives of the RNEA
+ * (Dynamics.cc:26-105) restricted to what each keyed channel reaches, the transposed stencils (core_rbdl.cpp:28-95), the Bezier
+ * value's partials with the implicit derivative of its Newton root (curve.cpp:43-93), D_param and D_traj -- from ONE evaluation of
+ * the per-sample arrays instead of 2F+1 objective columns. Agrees with the central-difference gradient of omo_eval_grad to its
+ * truncation error (~1e-7 relative at h = 1e-4). f0_out optional. OMO_UNSUPPORTED for scenes with IK handles and for an x whose
+ * key times are not ascending within a curve: call omo_eval_grad there. */
+omo_status omo_eval_grad_analytic(omo_ctx* ctx, const double* x, const int* free_idx, int F, double* f0_out, double* grad_out);
+/* Host-only (no GPU): the flattened device scene table of `scene` (optimo_b200/csrc/omo_scene.cuh: OmoDevScene, cap >= its size) and
+ * each joint's subtree end. For the CPU check of the analytic gradient's arithmetic (tests/native); not a compute path. */
+omo_status omo_debug_scene_table(const omo_scene_desc* scene, void* out, unsigned long long cap, int* sub_end_out);
 
 /* Column-sharded form for multi-GPU: evaluates columns [col_begin, col_begin+col_count) of the (2F+1)-column
  * perturbation list (column 0 = x, column 2k+1 = x + h e_k, column 2k+2 = x - h e_k) and leaves the values in

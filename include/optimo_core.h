@@ -80,6 +80,11 @@ int optimo_perform_optimization_gradient(void* h, int explicit_termination, cons
 
 /* Host-only (no GPU): generate + NVRTC-compile the scene-specialised objective kernel of the current scene
  * (include/omo.h: omo_jit_probe). Returns 0 when it compiled; `log` = stack placement summary and compiler log. */
+/* Next row N4: f and its analytic gradient (include/omo.h: omo_eval_grad_analytic); *analytic_used = 0 when the scene / x is outside its
+ * coverage and the finite-difference gradient was returned instead. */
+int optimo_calculate_analytic_gradient(void* h, double min_t, double max_t, const double* x, const double* x_original, int n, const int* free_idx, int F,
+                                       double* f0, double* grad, int* analytic_used);
+int optimo_debug_scene_table(void* h, void* out, unsigned long long cap, int* sub_end_out);   /* host-only, see omo_debug_scene_table */
 int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump_prefix, char* log, int cap);
 
 /* Record of the last solve's callbacks in call order (rows x (dim + 1): the free parameters, then f); off by default. */

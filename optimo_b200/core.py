@@ -106,6 +106,8 @@ _CORE_SIG = {
     "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
     "optimo_perform_optimization_gradient": (ci, [_vp, ci, cs, _dp, _ip]),
     "optimo_probe_specialised_kernel": (ci, [_vp, ci, ci, cs, cs, ci]),
+    "optimo_debug_scene_table": (ci, [_vp, _vp, C.c_ulonglong, _ip]),
+    "optimo_calculate_analytic_gradient": (ci, [_vp, cd, cd, _dp, _dp, ci, _ip, ci, _dp, _dp, _ip]),
     "optimo_record_solve_trace": (None, [_vp, ci]),
     "optimo_solve_trace_size": (ci, [_vp, _ip, _ip]),
     "optimo_get_solve_trace": (ci, [_vp, _dp]),
@@ -621,6 +623,23 @@ class Core:
         self._ck(_core.optimo_calculate_gradient(self.h, min_t, max_t, xp, op, xa.size, ip, idx.size, float(h), C.byref(f0),
                                                 g.ctypes.data_as(_dp), fpm.ctypes.data_as(_dp)))
         return f0.value, g, fpm
+
+    def CalculateAnalyticGradient(self, min_t, max_t, x, x_original, free_idx=None):
+        """Next row N4: (f0, grad[F], analytic_used) -- the analytic gradient, or the finite-difference one where it does not apply."""
+        xa, xp = _d(x)
+        oa, op = _d(x_original)
+        idx, ip = _i(self.free_indices() if free_idx is None else free_idx)
+        g = np.zeros(idx.size)
+        f0, used = C.c_double(0.0), C.c_int(0)
+        self._ck(_core.optimo_calculate_analytic_gradient(self.h, min_t, max_t, xp, op, xa.size, ip, idx.size, C.byref(f0), g.ctypes.data_as(_dp), C.byref(used)))
+        return f0.value, g, bool(used.value)
+
+    def debug_scene_table(self, nbytes):
+        """Host-only: (bytes of the flattened device scene table, sub_end[J]) for the CPU check of the analytic gradient's arithmetic."""
+        buf = C.create_string_buffer(nbytes)
+        sub_end = np.zeros(self.J, dtype=np.int32)
+        self._ck(_core.optimo_debug_scene_table(self.h, C.cast(buf, _vp), nbytes, sub_end.ctypes.data_as(_ip)))
+        return buf, sub_end
 
     def positions(self, min_t, max_t, x):
         xa, xp = _d(x)

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "omo_objective.cuh"
+#include "omo_adjoint_kernels.cuh"
 
 #include <chrono>
 
@@ -139,6 +140,12 @@ struct omo_ctx {
     double* d_self_out = nullptr;               // its device alias
     int self_out_cap = 0;
     unsigned long long self_launches = 0;
+
+    // analytic gradient (omo_adjoint_kernels.cuh)
+    int *d_sub_end = nullptr, *d_pos_of_cp = nullptr, *d_ci_of_pos = nullptr, *d_adj_m = nullptr;
+    double *d_adj_L = nullptr, *d_adj_G = nullptr, *d_adj_contrib = nullptr, *d_adj_gfull = nullptr, *d_adj_gout = nullptr, *d_oroot = nullptr;
+    size_t adj_cap = 0; int adj_F_cap = 0; int adj_max_sub = 0;
+    unsigned long long adj_calls = 0;
 
     // counters / timing
     unsigned long long* d_counters = nullptr;
@@ -685,7 +692,7 @@ omo_status ensure_outputs(omo_ctx* ctx)
 }
 
 // One candidate with per-sample outputs (used for the OptimizationCache, positions and p_original).
-omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig)
+omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig, double* d_root = nullptr)
 {
     omo_status st;
     if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
@@ -696,6 +703,7 @@ omo_status run_single_out(omo_ctx* ctx, const double* d_x, bool with_p_orig)
     fill_params(ctx, P);
     P.p_orig = with_p_orig ? ctx->d_p_orig : nullptr;
     P.o_q = ctx->d_oq; P.o_qd = ctx->d_oqd; P.o_qdd = ctx->d_oqdd; P.o_tau = ctx->d_otau; P.o_local = ctx->d_olocal; P.o_p = ctx->d_op;
+    P.o_root = d_root;
     return launch_objective(ctx, P, 1, true, true, ctx->d_f, ctx->d_terms);
 }
 
@@ -1053,6 +1061,9 @@ void omo_destroy(omo_ctx* ctx)
     if (ctx->d_Xfree) cudaFree(ctx->d_Xfree);
     if (ctx->d_inv_free) cudaFree(ctx->d_inv_free);
     if (ctx->d_single) cudaFree(ctx->d_single);
+    { void* ap[] = {ctx->d_sub_end, ctx->d_pos_of_cp, ctx->d_ci_of_pos, ctx->d_adj_m, ctx->d_adj_L, ctx->d_adj_G, ctx->d_adj_contrib, ctx->d_adj_gfull,
+                    ctx->d_adj_gout, ctx->d_oroot};
+      for (void* q : ap) if (q) cudaFree(q); }
     if (ctx->d_self_dparam) cudaFree(ctx->d_self_dparam);
     if (ctx->d_self_counter) cudaFree(ctx->d_self_counter);
     if (ctx->h_self_out) cudaFreeHost(ctx->h_self_out);
@@ -1532,6 +1543,123 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     }
     if (fpm_out) std::copy(ctx->h_cols.begin() + 1, ctx->h_cols.end(), fpm_out);
     return omo_grad_from_columns(ctx->h_cols.data(), F, h, f0_out, grad_out);
+}
+
+omo_status omo_eval_grad_analytic(omo_ctx* ctx, const double* x, const int* free_idx, int F, double* f0_out, double* grad_out)
+{
+    DeviceLock device_lock(ctx);
+    if (!ctx || (!x && ctx->D > 0) || F < 0 || (F > 0 && (!free_idx || !grad_out))) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    for (int k = 0; k < F; ++k) if (free_idx[k] < 0 || free_idx[k] >= ctx->D) return fail(ctx, OMO_BAD_ARG, "free index outside the descriptor");
+    if (ctx->n_ik > 0) return fail(ctx, OMO_UNSUPPORTED, "the analytic gradient does not cover IK handles (the angles of an IK chain come out of an iterative solve); use omo_eval_grad");
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
+    const int N = ctx->N_s, nk = ctx->hs.n_keyed, J = ctx->J;
+    // tables, once per context
+    if (!ctx->d_sub_end) {
+        std::vector<int> sub_end(J), ci_of_pos(std::max(ctx->n_cp, 1), -1), pos_of_cp(std::max(ctx->n_cp, 1), 0);
+        for (int j = J - 1; j >= 0; --j) {
+            sub_end[j] = j + 1;
+            for (int k = j + 1; k < J; ++k) if (ctx->hs.parent[k] == j) sub_end[j] = std::max(sub_end[j], sub_end[k]);
+        }
+        ctx->adj_max_sub = 1;
+        for (int i = 0; i < nk; ++i) {
+            const int ch = ctx->hs.grp_list[i], j = ch / 3;
+            ctx->adj_max_sub = std::max(ctx->adj_max_sub, sub_end[j] - j);
+            for (int p = 0; p < ctx->hs.chan_n[ch]; ++p) ci_of_pos[ctx->hs.chan_pos[ch] + p] = i;
+        }
+        for (int pos = 0; pos < ctx->n_cp; ++pos) pos_of_cp[ctx->cp_of_pos[pos]] = pos;
+        if ((st = upload(ctx, &ctx->d_sub_end, sub_end)) != OMO_OK) return st;
+        if ((st = upload(ctx, &ctx->d_ci_of_pos, ci_of_pos)) != OMO_OK) return st;
+        if ((st = upload(ctx, &ctx->d_pos_of_cp, pos_of_cp)) != OMO_OK) return st;
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // the vectors above are locals
+    }
+    const size_t cells = (size_t)std::max(nk, 1) * N;
+    if (cells > ctx->adj_cap) {
+        if ((st = dev_alloc(ctx, &ctx->d_adj_L, 3 * cells)) != OMO_OK) return st;
+        if ((st = dev_alloc(ctx, &ctx->d_adj_G, cells)) != OMO_OK) return st;
+        if ((st = dev_alloc(ctx, &ctx->d_adj_contrib, 10 * cells)) != OMO_OK) return st;
+        if ((st = dev_alloc(ctx, &ctx->d_adj_m, cells)) != OMO_OK) return st;
+        if ((st = dev_alloc(ctx, &ctx->d_adj_gfull, (size_t)std::max(ctx->D, 1))) != OMO_OK) return st;
+        if ((st = dev_alloc(ctx, &ctx->d_oroot, (size_t)3 * N)) != OMO_OK) return st;
+        ctx->adj_cap = cells;
+    }
+    if (F > ctx->adj_F_cap) { if ((st = dev_alloc(ctx, &ctx->d_adj_gout, (size_t)F)) != OMO_OK) return st; ctx->adj_F_cap = F; }
+    if (F > ctx->free_cap) { if ((st = dev_alloc(ctx, &ctx->d_free, (size_t)F)) != OMO_OK) return st; ctx->free_cap = F; ctx->free_uploaded.clear(); }
+    if (F > 0 && (ctx->free_uploaded.size() != (size_t)F || !std::equal(ctx->free_uploaded.begin(), ctx->free_uploaded.end(), free_idx))) {
+        ctx->free_uploaded.assign(free_idx, free_idx + F);
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_free, ctx->free_uploaded.data(), (size_t)F * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    // the evaluated point: f, and the per-sample q, qd, qdd, tau of the OptimizationCache (per-sample-output kernel, full tree)
+    OMO_CUDA(cudaMemcpyAsync(ctx->d_X, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    const bool traj = ctx->w_traj != 0.0;
+    if ((st = run_single_out(ctx, ctx->d_X, traj, ctx->d_oroot)) != OMO_OK) return st;
+    unsigned flag0 = 1u;
+    double f0 = 0.0;
+    OMO_CUDA(cudaMemcpyAsync(&flag0, ctx->d_flags, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+    OMO_CUDA(cudaMemcpyAsync(&f0, ctx->d_f, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    omo::OmoAdjParams A;
+    std::memset(&A, 0, sizeof(A));
+    A.sub_end = ctx->d_sub_end; A.q = ctx->d_oq; A.qd = ctx->d_oqd; A.qdd = ctx->d_oqdd; A.tau = ctx->d_otau;
+    A.root_e = ctx->hs.dyn[0] ? ctx->d_oroot : nullptr;
+    A.wcost = ctx->d_wcost; A.p_orig = traj ? ctx->d_p_orig : nullptr; A.tgrid = ctx->d_tgrid; A.w_traj = ctx->w_traj; A.dt = ctx->dt;
+    A.N_s = N; A.n_keyed = nk; A.n_cp = ctx->n_cp; A.D = ctx->D; A.cyclic = ctx->cyclic;
+    A.x = ctx->d_X; A.cp_of_pos = ctx->d_cp_of_pos; A.first_of_pos = ctx->d_first_of_pos; A.last_of_pos = ctx->d_last_of_pos;
+    A.pos_of_cp = ctx->d_pos_of_cp; A.ci_of_pos = ctx->d_ci_of_pos;
+    A.L = ctx->d_adj_L; A.G = ctx->d_adj_G; A.contrib = ctx->d_adj_contrib; A.seg_m = ctx->d_adj_m; A.gfull = ctx->d_adj_gfull;
+    A.free_idx = ctx->d_free; A.F = F; A.x0 = ctx->d_x0; A.wparam = ctx->d_wparam; A.gout = ctx->d_adj_gout;
+    if (nk > 0) {
+        const long long nt = 3LL * nk * N;
+        const unsigned gb = (unsigned)((nt + 127) / 128);
+        if (ctx->adj_max_sub <= 16) omo::adj_tangent_kernel<16><<<gb, 128, 0, ctx->stream>>>(A);
+        else if (ctx->adj_max_sub <= 64) omo::adj_tangent_kernel<64><<<gb, 128, 0, ctx->stream>>>(A);
+        else omo::adj_tangent_kernel<OMO_MAX_JOINTS><<<gb, 128, 0, ctx->stream>>>(A);
+        OMO_CUDA(cudaGetLastError());
+        const unsigned gc = (unsigned)((cells + 127) / 128);
+        omo::adj_stencil_kernel<<<gc, 128, 0, ctx->stream>>>(A);
+        omo::adj_bezier_kernel<<<gc, 128, 0, ctx->stream>>>(A);
+        OMO_CUDA(cudaGetLastError());
+        ctx->launches += 3;
+    }
+    if (ctx->n_cp > 0) {
+        omo::adj_reduce_kernel<<<(5 * ctx->n_cp + 127) / 128, 128, 0, ctx->stream>>>(A);
+        OMO_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+    }
+    if (F > 0) {
+        omo::adj_output_kernel<<<(F + 127) / 128, 128, 0, ctx->stream>>>(A);
+        OMO_CUDA(cudaGetLastError());
+        OMO_CUDA(cudaMemcpyAsync(grad_out, ctx->d_adj_gout, (size_t)F * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        ctx->launches += 1;
+    }
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    if ((flag0 & 1u) == 0u)
+        return fail(ctx, OMO_UNSUPPORTED, "a curve's key times are not in ascending order at this x: its segments are found in list order (curve.cpp:100-128), which the analytic gradient does not cover; use omo_eval_grad");
+    if (f0_out) *f0_out = f0;
+    ctx->adj_calls += 1;
+    return OMO_OK;
+}
+
+omo_status omo_debug_scene_table(const omo_scene_desc* scene, void* out, unsigned long long cap, int* sub_end_out)
+{
+    if (!scene || !out || cap < sizeof(OmoDevScene)) return OMO_BAD_ARG;
+    omo_ctx* ctx = new omo_ctx();
+    omo_status st = build_tables(ctx, scene);
+    if (st == OMO_OK) {
+        ctx->dt = 0.2;
+        refresh_residues(ctx);
+        std::memcpy(out, &ctx->hs, sizeof(OmoDevScene));
+        if (sub_end_out) {
+            const int J = ctx->J;
+            for (int j = J - 1; j >= 0; --j) {
+                sub_end_out[j] = j + 1;
+                for (int k = j + 1; k < J; ++k) if (ctx->hs.parent[k] == j) sub_end_out[j] = std::max(sub_end_out[j], sub_end_out[k]);
+            }
+        }
+    }
+    delete ctx;
+    return st;
 }
 
 omo_status omo_grad_sparsity(const omo_ctx* ctx, unsigned long long* out2)

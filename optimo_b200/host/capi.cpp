@@ -195,6 +195,23 @@ int optimo_perform_optimization_gradient(void* h, int explicit_termination, cons
     });
 }
 
+int optimo_debug_scene_table(void* h, void* out, unsigned long long cap, int* sub_end_out)
+{
+    int status = 1;
+    const int rc = guarded([&] { status = C(h)->DebugSceneTable(out, cap, sub_end_out); });
+    return rc ? rc : status;
+}
+int optimo_calculate_analytic_gradient(void* h, double min_t, double max_t, const double* x, const double* x_original, int n, const int* free_idx, int F,
+                                       double* f0, double* grad, int* analytic_used)
+{
+    return guarded([&] {
+        VecN g;
+        bool used = false;
+        *f0 = C(h)->CalculateFullObjectiveAndAnalyticGradient(min_t, max_t, VecN(x, x + n), VecN(x_original, x_original + n), std::vector<int>(free_idx, free_idx + F), &g, &used);
+        std::copy(g.begin(), g.end(), grad);
+        if (analytic_used) *analytic_used = used ? 1 : 0;
+    });
+}
 int optimo_probe_specialised_kernel(void* h, int fk, int count, const char* dump_prefix, char* log, int cap)
 {
     int status = 0;

@@ -413,6 +413,11 @@ omo_ctx* Core::Engine()
     d.n_ik = static_cast<int>(iks.size()); d.ik_root = ik_root.data(); d.ik_end = ik_end.data();
     d.n_channels = static_cast<int>(chan_const.size()); d.chan_const = chan_const.data(); d.chan_first_cp = first_cp.data();
     d.chan_n_cp = n_cp_ch.data(); d.n_cp = cp_total; d.chain = chain.data();
+    if (probe_only_ && debug_table_out_) {
+        // host-only: the flattened device scene table (include/omo.h: omo_debug_scene_table); no device is touched
+        probe_status_ = static_cast<int>(omo_debug_scene_table(&d, debug_table_out_, debug_table_cap_, debug_sub_end_out_));
+        return nullptr;
+    }
     if (probe_only_) {
         // host-only check of the scene-specialised kernel (include/omo.h: omo_jit_probe); no device is touched
         std::vector<char> log(1 << 16, 0);
@@ -443,6 +448,18 @@ int Core::ProbeSpecialisedKernel(bool fk, int flags, const std::string& dump_pre
     probe_only_ = false;
     engine_ = keep;
     if (log) *log = probe_log_;
+    return probe_status_;
+}
+
+int Core::DebugSceneTable(void* out, unsigned long long cap, int* sub_end_out)
+{
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    omo_ctx* keep = engine_;
+    engine_ = nullptr;
+    probe_only_ = true; debug_table_out_ = out; debug_table_cap_ = cap; debug_sub_end_out_ = sub_end_out;
+    try { Engine(); } catch (...) { probe_only_ = false; debug_table_out_ = nullptr; engine_ = keep; throw; }
+    probe_only_ = false; debug_table_out_ = nullptr;
+    engine_ = keep;
     return probe_status_;
 }
 
@@ -533,6 +550,24 @@ double Core::CalculateFullObjectiveAndGradient(double min_t, double max_t, const
         Check(omo_eval_grad(engine_, x.data(), free_indices.data(), F, h, &f0, grad->data(), f_plus_minus ? f_plus_minus->data() : nullptr),
               "omo_eval_grad");
     }
+    NoteEvaluated(x, min_t, max_t);
+    return f0;
+}
+
+double Core::CalculateFullObjectiveAndAnalyticGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
+                                                       const std::vector<int>& free_indices, VecN* grad, bool* analytic_used)
+{
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    SyncEngine(min_t, max_t, x_original);
+    if (x.size() != x_original.size()) throw std::invalid_argument("x has the wrong length");
+    const int F = static_cast<int>(free_indices.size());
+    grad->assign(F, 0.0);
+    double f0 = 0.0;
+    const omo_status st = omo_eval_grad_analytic(engine_, x.data(), free_indices.data(), F, &f0, grad->data());
+    if (analytic_used) *analytic_used = st == OMO_OK;
+    if (st == OMO_UNSUPPORTED)   // IK handles / unsorted keys: the finite-difference gradient covers them
+        return CalculateFullObjectiveAndGradient(min_t, max_t, x, x_original, free_indices, 1e-4, grad);
+    Check(st, "omo_eval_grad_analytic");
     NoteEvaluated(x, min_t, max_t);
     return f0;
 }

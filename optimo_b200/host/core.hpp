@@ -69,6 +69,10 @@ public:
     /// NEW: f(x) and its central-difference gradient on the free dofs.
     double CalculateFullObjectiveAndGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
                                              const std::vector<int>& free_indices, double h, VecN* grad, VecN* f_plus_minus = nullptr);
+    /// Next row N4: f(x) and its ANALYTIC gradient on the free dofs (include/omo.h: omo_eval_grad_analytic); scenes it does not
+    /// cover (IK handles, unsorted key times) get the finite-difference gradient instead (*analytic_used tells which).
+    double CalculateFullObjectiveAndAnalyticGradient(double min_t, double max_t, const VecN& x, const VecN& x_original,
+                                                     const std::vector<int>& free_indices, VecN* grad, bool* analytic_used = nullptr);
     /// (C, D_param, D_traj) of the last CalculateFullObjective call.
     omo_terms last_terms_{0, 0, 0};
 
@@ -138,6 +142,8 @@ public:
     /// Generates and NVRTC-compiles the scene-specialised objective kernel of the current scene on the host (no GPU
     /// needed); returns the omo_status, `log` gets the placement summary + compiler log. See omo_jit_probe.
     int ProbeSpecialisedKernel(bool fk, int flags, const std::string& dump_prefix, std::string* log);   // flags: omo_jit_probe's `count`
+    /// Host-only: the flattened device scene table of the current scene (omo_debug_scene_table), for tests/native.
+    int DebugSceneTable(void* out, unsigned long long cap, int* sub_end_out);
     /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
     void InitializeDynamicsModel();
 
@@ -172,6 +178,7 @@ private:
     bool probe_only_ = false;
     int probe_fk_ = 0, probe_count_ = 0, probe_status_ = 0;
     std::string probe_prefix_, probe_log_;
+    void* debug_table_out_ = nullptr; unsigned long long debug_table_cap_ = 0; int* debug_sub_end_out_ = nullptr;
     int device_ = 0;
 
     std::mutex optimization_cache_mutex_;

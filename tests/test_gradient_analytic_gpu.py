@@ -1,0 +1,93 @@
+"""Next row N4: the analytic gradient (omo_eval_grad_analytic) against the central-difference gradient
+of the same objective on the GPU and against the oracle's ("oracle = the existing FD gradient at 1e-6 relative").
+The arithmetic itself is checked on the CPU in tests/test_adjoint_math.py."""
+import numpy as np
+import pytest
+
+from conftest import load_scene, scene_path
+
+from optimo_b200 import synthetic
+from optimo_b200.core import Core
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-6     # of the largest gradient entry: the central difference at h = 1e-4 is itself only that accurate (h^2 f''' / 6)
+
+
+def _scene(name):
+    if name == "stick240":
+        return synthetic.stick_240(load_scene("stick-figure"))
+    if name == "tree24":
+        return synthetic.tree_scene(n_joints=24, n_frames=60)
+    return load_scene(name)
+
+
+@pytest.mark.parametrize("name,w_traj,kernels,cyclic", [
+    ("stick-figure", 0.0, [], False), ("stick-figure", 12.5, [(1.0, 20.0, 2.6)], False), ("stick-figure", 12.5, [], True),
+    ("fox-tail", 0.0, [], False), ("fox-tail", 3.0, [(1.0, 10.0, 1.0)], True), ("stick240", 12.5, [], False), ("tree24", 1.0, [], False)])
+def test_analytic_gradient_matches_the_finite_difference_gradient(oracle_port, name, w_traj, kernels, cyclic):
+    scene = _scene(name)
+    c = Core(scene)
+    c.UpdateGlobalWeight(w_traj); c.set_kernels(kernels); c.set_cyclic(cyclic)
+    x0 = c.GetDescriptor()
+    x = synthetic.perturbed_candidates(x0, 1, first=5)[0]
+    lo, hi = c.window
+    f_an, g_an, used = c.CalculateAnalyticGradient(lo, hi, x, x0)
+    assert used
+    f_fd, g_fd, _ = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
+    assert abs(f_an - f_fd) <= 1e-12 * abs(f_fd)            # the per-sample-output kernel (table-driven) vs the specialised one
+    scale = max(float(np.max(np.abs(g_fd))), 1.0)
+    err = float(np.max(np.abs(g_an - g_fd)))
+    assert err <= REL * scale + 2e-14 * abs(f_fd) / 2e-4, (err, scale)
+    # every free parameter kind is covered: theta, t_b, t_f entries all carry signal somewhere
+    idx = c.free_indices()
+    for field in (2, 3, 4):
+        sel = idx % 5 == field
+        assert np.max(np.abs(g_an[sel])) > 0
+    if name in ("stick-figure", "fox-tail"):
+        o = oracle_port.Oracle(scene, "port")
+        o.set_weight_trajectory(w_traj); o.set_kernels(kernels); o.set_cyclic(cyclic)
+        o.update_original(x0)
+        fo, go, _ = o.gradient(x, h=1e-4)
+        assert np.max(np.abs(g_an - go)) <= REL * max(float(np.max(np.abs(go))), 1.0) + 2e-14 * abs(fo) / 2e-4
+
+
+def test_analytic_gradient_with_free_times_and_values():
+    """t and v of the control points freed as well (the reference's default freezes them, core.cpp:83-88): the derivative with
+    respect to a key time goes through the implicit root of BOTH adjacent segments."""
+    c = Core(scene_path("stick-figure"))
+    x0 = c.GetDescriptor()
+    c.freezed_dofs_ = np.zeros(x0.size, dtype=np.int32)
+    x = synthetic.perturbed_candidates(x0, 1, first=2)[0]
+    lo, hi = c.window
+    f_an, g_an, used = c.CalculateAnalyticGradient(lo, hi, x, x0)
+    f_fd, g_fd, _ = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
+    assert used and g_an.size == x0.size
+    # values, tangents and handle lengths: smooth, compared entry by entry
+    field = np.arange(x0.size) % 5
+    scale = max(float(np.max(np.abs(g_fd[field != 0]))), 1.0)
+    assert np.max(np.abs(g_an[field != 0] - g_fd[field != 0])) <= 2e-6 * scale
+    # key times: one that crosses a sample time switches that sample's segment -- f is only piecewise smooth in t, and the shipped
+    # keys sit on whole frames, i.e. exactly ON sample times. The central difference is meaningful where its one-sided halves agree.
+    _, _, fpm = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
+    fwd, bwd = (fpm[:, 0] - f_fd) / 1e-4, (f_fd - fpm[:, 1]) / 1e-4
+    ok = (field == 0) & (np.abs(fwd - bwd) <= 1e-2 * np.maximum(np.abs(g_fd), 1.0))
+    assert ok.sum() >= 5
+    assert np.max(np.abs(g_an[ok] - g_fd[ok])) <= 1e-4 * max(float(np.max(np.abs(g_fd[ok]))), 1.0)
+
+
+def test_scenes_outside_the_analytic_gradient_fall_back_to_finite_differences():
+    """IK handles (the chain's angles come out of an iterative solve) and an x whose key times are out of order (list-order segment
+    search) are answered by the finite-difference gradient, and the caller is told so."""
+    c = Core(scene_path("conductor"))
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    f, g, used = c.CalculateAnalyticGradient(lo, hi, x0, x0)
+    f2, g2, _ = c.CalculateGradient(lo, hi, x0, x0)
+    assert not used and f == f2 and np.array_equal(g, g2)
+    s = Core(scene_path("stick-figure"))
+    xs = s.GetDescriptor()
+    x = xs.copy(); x[0] = x[5] + 0.25
+    f, g, used = s.CalculateAnalyticGradient(*s.window, x, xs)
+    f2, g2, _ = s.CalculateGradient(*s.window, x, xs)
+    assert not used and f == f2 and np.array_equal(g, g2)
