@@ -76,6 +76,12 @@ int optimo_perform_optimization(void* h, int explicit_termination, double* final
 /* The same solve with a gradient-based NLopt algorithm ("LD_LBFGS", "LD_SLSQP", "LD_MMA", "LD_TNEWTON" ...; NULL = LD_LBFGS), as
  * nloptutil::unconstrained::grad_based::bounded::solve sets one up (external/nlopt-util/include/nlopt-util.hpp:226-274): every
  * callback returns f and the central-difference gradient over the free dofs from one GPU batch. */
+/* Batched BOBYQA start: the solver's first 2M+1 interpolation points -- which do not depend on any function value
+ * (external/nlopt/src/algs/bobyqa/bobyqa.c prelim_) -- are predicted, evaluated as ONE GPU batch and served to the callback from a cache
+ * keyed on the bits of x. Default on; the iterates are identical either way. optimo_last_solve_batched: callbacks served that way. */
+void optimo_set_batched_start(void* h, int on);
+int optimo_last_solve_batched(void* h);
+/* algorithm: any gradient-based NLopt algorithm name; a "+analytic" suffix ("LD_SLSQP+analytic") takes the analytic gradient (N4) */
 int optimo_perform_optimization_gradient(void* h, int explicit_termination, const char* algorithm, double* final_value, int* evals);
 
 /* Host-only (no GPU): generate + NVRTC-compile the scene-specialised objective kernel of the current scene

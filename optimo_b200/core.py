@@ -105,6 +105,8 @@ _CORE_SIG = {
     "optimo_get_stop_optimization": (ci, [_vp]),
     "optimo_perform_optimization": (ci, [_vp, ci, _dp, _ip]),
     "optimo_perform_optimization_gradient": (ci, [_vp, ci, cs, _dp, _ip]),
+    "optimo_set_batched_start": (None, [_vp, ci]),
+    "optimo_last_solve_batched": (ci, [_vp]),
     "optimo_probe_specialised_kernel": (ci, [_vp, ci, ci, cs, cs, ci]),
     "optimo_debug_scene_table": (ci, [_vp, _vp, C.c_ulonglong, _ip]),
     "optimo_calculate_analytic_gradient": (ci, [_vp, cd, cd, _dp, _dp, ci, _ip, ci, _dp, _dp, _ip]),
@@ -726,10 +728,18 @@ class Core:
         self._ck(_core.optimo_perform_optimization(self.h, int(explicit_termination), C.byref(v), C.byref(n)))
         return v.value, n.value
 
-    def PerformOptimizationWithGradient(self, explicit_termination=False, algorithm="LD_LBFGS"):
-        """Gradient-based solve (finite-difference gradient on the GPU). Returns (final objective value, function evaluations)."""
+    def set_batched_start(self, on):
+        """Batched BOBYQA start: the solver's first 2M+1 points as one GPU batch (default on)."""
+        _core.optimo_set_batched_start(self.h, int(bool(on)))
+
+    @property
+    def last_solve_batched(self):
+        return _core.optimo_last_solve_batched(self.h)
+
+    def PerformOptimizationWithGradient(self, explicit_termination=False, algorithm="LD_LBFGS", analytic=False):
+        """Gradient-based solve (finite-difference gradient on the GPU, or the analytic one). Returns (final objective value, function evaluations)."""
         v, n = C.c_double(0.0), C.c_int(0)
-        self._ck(_core.optimo_perform_optimization_gradient(self.h, int(explicit_termination), algorithm.encode(), C.byref(v), C.byref(n)))
+        self._ck(_core.optimo_perform_optimization_gradient(self.h, int(explicit_termination), (algorithm + ("+analytic" if analytic else "")).encode(), C.byref(v), C.byref(n)))
         return v.value, n.value
 
     def probe_specialised_kernel(self, fk=False, count=False, dump_prefix=None, self_preparing=False):

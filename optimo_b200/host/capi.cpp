@@ -186,10 +186,17 @@ int optimo_perform_optimization(void* h, int explicit_termination, double* final
     });
 }
 
+void optimo_set_batched_start(void* h, int on) { C(h)->batched_start_ = on != 0; }
+int optimo_last_solve_batched(void* h) { return C(h)->last_solve_batched_; }
 int optimo_perform_optimization_gradient(void* h, int explicit_termination, const char* algorithm, double* final_value, int* evals)
 {
     return guarded([&] {
-        C(h)->PerformOptimizationWithGradient(explicit_termination != 0, algorithm ? algorithm : "LD_LBFGS");
+        // "LD_SLSQP+analytic": the same algorithm over the analytic gradient (next row N4)
+        std::string alg = algorithm ? algorithm : "LD_LBFGS";
+        bool analytic = false;
+        const size_t plus = alg.find("+analytic");
+        if (plus != std::string::npos) { analytic = true; alg.erase(plus); }
+        C(h)->PerformOptimizationWithGradient(explicit_termination != 0, alg, analytic);
         if (final_value) *final_value = C(h)->last_solve_value_;
         if (evals) *evals = C(h)->last_solve_evals_;
     });

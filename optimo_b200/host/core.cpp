@@ -2,6 +2,7 @@
 #include "core.hpp"
 
 #include <algorithm>
+#include <cstring>
 #include <cassert>
 #include <cstdlib>
 #include <fstream>
@@ -517,6 +518,12 @@ void Core::NoteEvaluated(const VecN& x, double min_t, double max_t)
     last_x_ = x; last_min_t_ = min_t; last_max_t_ = max_t; have_last_ = true; cache_stale_ = true;
 }
 
+void Core::NoteEvaluatedFromCache(const VecN& x, double min_t, double max_t)
+{
+    std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+    NoteEvaluated(x, min_t, max_t);
+}
+
 void Core::CalculateFullObjectiveBatch(double min_t, double max_t, const double* X, int B, const VecN& x_original, double* f_out,
                                        omo_terms* terms_out)
 {
@@ -674,9 +681,21 @@ double EvaluateObjective(const std::vector<double>& x, std::vector<double>& grad
         throw forced_stop();
     }
     d->evaluations += 1;
+    if (!d->start_cache_x.empty() && !(d->want_gradient && !grad.empty())) {
+        // batched start: the solver's x, bit for bit, among the points evaluated before it began?
+        for (size_t b = 0; b < d->start_cache_x.size(); ++b) {
+            if (d->start_cache_x[b].size() == x.size() && std::memcmp(d->start_cache_x[b].data(), x.data(), x.size() * sizeof(double)) == 0) {
+                d->start_cache_hits += 1;
+                core.NoteEvaluatedFromCache(full, d->min_t, d->max_t);
+                return d->start_cache_f[b];
+            }
+        }
+    }
     if (d->want_gradient && !grad.empty()) {
         VecN g;
-        const double f = core.CalculateFullObjectiveAndGradient(d->min_t, d->max_t, full, d->x_original, d->free_indices, d->gradient_step, &g);
+        const double f = d->analytic_gradient
+                             ? core.CalculateFullObjectiveAndAnalyticGradient(d->min_t, d->max_t, full, d->x_original, d->free_indices, &g)
+                             : core.CalculateFullObjectiveAndGradient(d->min_t, d->max_t, full, d->x_original, d->free_indices, d->gradient_step, &g);
         std::copy(g.begin(), g.end(), grad.begin());
         return f;
     }

@@ -59,7 +59,9 @@ public:
     /// nloptutil::unconstrained::grad_based::bounded::solve would set it up (nlopt-util.hpp:226-274) -- every callback
     /// returns f and the central-difference gradient over the free dofs from one sparse GPU batch (include/omo.h:
     /// omo_eval_grad). Bounds on t_b / t_f are pulled in by the difference step so that x +- h stays feasible.
-    void PerformOptimizationWithGradient(bool explicit_termination = false, const std::string& algorithm = "LD_LBFGS");
+    /// analytic = true: the gradient comes from omo_eval_grad_analytic (next row N4) -- one evaluation of the per-sample arrays
+    /// instead of 2F+1 objective columns; scenes it does not cover (IK handles) silently keep the finite-difference gradient.
+    void PerformOptimizationWithGradient(bool explicit_termination = false, const std::string& algorithm = "LD_LBFGS", bool analytic = false);
 
     /// core_rbdl.cpp:348-401. Like the reference it leaves the object at `x`.
     double CalculateFullObjective(double min_t, double max_t, const VecN& x, const VecN& x_original);
@@ -75,6 +77,8 @@ public:
                                                      const std::vector<int>& free_indices, VecN* grad, bool* analytic_used = nullptr);
     /// (C, D_param, D_traj) of the last CalculateFullObjective call.
     omo_terms last_terms_{0, 0, 0};
+    /// What an evaluation leaves behind (object at x, cache stale) for a value that was served from the batched start.
+    void NoteEvaluatedFromCache(const VecN& x, double min_t, double max_t);
 
     void ReadJson(const std::string& file_path);          // core_io.cpp:154-163
     void ReadJsonString(const std::string& json_text);    // ApplyJsonToScene + InitializeDynamicsModel
@@ -147,11 +151,15 @@ public:
     /// Called after any structural change of object_ (core_rbdl.cpp:200-262): drops the engine.
     void InitializeDynamicsModel();
 
-    void Solve(bool explicit_termination, const char* algorithm, bool want_gradient);   // body of both PerformOptimization forms
+    void Solve(bool explicit_termination, const char* algorithm, bool want_gradient, bool analytic = false);   // body of both PerformOptimization forms
     /// Result of the last PerformOptimization (function value, evaluations).
     double last_solve_value_ = 0.0;
     int last_solve_evals_ = 0;
     std::string last_solve_status_;
+    /// Batched BOBYQA start: evaluate the solver's first 2M+1 points as one GPU batch (default on; results are bit-identical to
+    /// the serial start). last_solve_batched_ = callbacks of the last solve that were served from that batch.
+    bool batched_start_ = true;
+    int last_solve_batched_ = 0;
     /// Optional record of every callback of the last solve, in call order: M free parameters then f per row
     /// (used to replay a solve against another implementation of the objective).
     bool record_solve_trace_ = false;
@@ -198,8 +206,13 @@ struct EvaluateObjectiveData {
     VecN x_initial;    // #{full dofs}: values of the frozen dofs (Y * x_initial, core_opt.cpp:121)
     std::vector<int> free_indices;  // X: free -> full
     bool want_gradient = false;
+    bool analytic_gradient = false;   // next row N4: omo_eval_grad_analytic instead of the 2F+1 finite-difference columns
     double gradient_step = 1e-4;
     int evaluations = 0;
+    // batched BOBYQA start (core_opt.cpp): predicted points in the callback's parameter space and their values
+    std::vector<VecN> start_cache_x;
+    std::vector<double> start_cache_f;
+    int start_cache_hits = 0;
 };
 double EvaluateObjective(const std::vector<double>& x, std::vector<double>& grad, void* data);
 

@@ -122,15 +122,81 @@ double trampoline(unsigned n, const double* x, double* grad, void* p)
 
 }  // namespace
 
-void Core::PerformOptimization(bool explicit_termination) { Solve(explicit_termination, "LN_BOBYQA", false); }
-
-void Core::PerformOptimizationWithGradient(bool explicit_termination, const std::string& algorithm)
+// The first 2n+1 points BOBYQA evaluates do not depend on any function value: x0 and x0 +- rho e_i, shifted where a bound is
+// nearer than rho (external/nlopt/src/algs/bobyqa/bobyqa.c: the bound preparation of bobyqa() :3205-3257, prelim_ :1822-1868,
+// NLopt's rescaling to equal initial steps :3093-3117 with src/util/rescale.c:29-71; reached from optimize.c:692-706 with
+// npt = 2n+1). This restates that arithmetic operation for operation -- same IEEE doubles, this file is built without FMA
+// contraction -- so that the points can be evaluated as ONE batch on the GPU before the solver starts.
+// A prediction that is off in a single bit simply never matches the solver's x and costs nothing but the unused evaluation.
+std::vector<VecN> PredictBobyqaStart(const VecN& x0, const VecN& lb, const VecN& ub, const VecN& dx)
 {
-    if (algorithm.size() < 2 || algorithm[1] != 'D') throw std::invalid_argument("PerformOptimizationWithGradient needs a gradient-based (LD_ / GD_) NLopt algorithm");
-    Solve(explicit_termination, algorithm.c_str(), true);
+    const size_t n = x0.size();
+    std::vector<VecN> pts;
+    if (n < 2) return pts;
+    VecN s(n, 1.0);
+    {
+        size_t i = 1;
+        for (; i < n && dx[i] == dx[i - 1]; ++i) {}
+        if (i < n) for (i = 1; i < n; ++i) s[i] = dx[i] / dx[0];
+    }
+    VecN x(n), xl(n), xu(n), sl(n), su(n);
+    for (size_t j = 0; j < n; ++j) {
+        if (s[j] == 0.0 || !std::isfinite(s[j])) return pts;
+        x[j] = x0[j] / s[j]; xl[j] = lb[j] / s[j]; xu[j] = ub[j] / s[j];
+        if (xl[j] > xu[j]) std::swap(xl[j], xu[j]);
+    }
+    const double rhobeg = std::fabs(dx[0] / s[0]);
+    for (size_t j = 0; j < n; ++j) {
+        const double temp = xu[j] - xl[j];
+        if (temp < rhobeg + rhobeg) return pts;   // BOBYQA refuses this itself
+        sl[j] = xl[j] - x[j];
+        su[j] = xu[j] - x[j];
+        if (sl[j] >= -rhobeg) {
+            if (sl[j] >= 0.0) { x[j] = xl[j]; sl[j] = 0.0; su[j] = temp; }
+            else { x[j] = xl[j] + rhobeg; sl[j] = -rhobeg; su[j] = std::max(xu[j] - x[j], rhobeg); }
+        } else if (su[j] <= rhobeg) {
+            if (su[j] <= 0.0) { x[j] = xu[j]; sl[j] = -temp; su[j] = 0.0; }
+            else { x[j] = xu[j] - rhobeg; sl[j] = std::min(xl[j] - x[j], -rhobeg); su[j] = rhobeg; }
+        }
+    }
+    const VecN xbase = x;
+    VecN stepa_of(n, 0.0);
+    for (size_t nf = 1; nf <= 2 * n + 1; ++nf) {
+        VecN xpt(n, 0.0);
+        const size_t nfm = nf - 1;
+        if (nfm >= 1 && nfm <= n) {
+            double stepa = rhobeg;
+            if (su[nfm - 1] == 0.0) stepa = -stepa;
+            xpt[nfm - 1] = stepa;
+            stepa_of[nfm - 1] = stepa;
+        } else if (nfm > n) {
+            const size_t nfx = nfm - n;
+            double stepb = -rhobeg;
+            if (sl[nfx - 1] == 0.0) stepb = std::min(2.0 * rhobeg, su[nfx - 1]);
+            if (su[nfx - 1] == 0.0) stepb = std::max(-2.0 * rhobeg, sl[nfx - 1]);
+            xpt[nfx - 1] = stepb;
+        }
+        VecN p(n);
+        for (size_t j = 0; j < n; ++j) {
+            double v = std::min(std::max(xl[j], xbase[j] + xpt[j]), xu[j]);
+            if (xpt[j] == sl[j]) v = xl[j];
+            if (xpt[j] == su[j]) v = xu[j];
+            p[j] = v * s[j];   // nlopt_unscale: what the callback receives
+        }
+        pts.push_back(p);
+    }
+    return pts;
 }
 
-void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gradient)
+void Core::PerformOptimization(bool explicit_termination) { Solve(explicit_termination, "LN_BOBYQA", false); }
+
+void Core::PerformOptimizationWithGradient(bool explicit_termination, const std::string& algorithm, bool analytic)
+{
+    if (algorithm.size() < 2 || algorithm[1] != 'D') throw std::invalid_argument("PerformOptimizationWithGradient needs a gradient-based (LD_ / GD_) NLopt algorithm");
+    Solve(explicit_termination, algorithm.c_str(), true, analytic);
+}
+
+void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gradient, bool analytic)
 {
     stop_optimization_ = false;
     constexpr int dim = 5;
@@ -164,6 +230,7 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     data.x_original = x_original;
     data.x_initial = x_initial;
     data.want_gradient = want_gradient;
+    data.analytic_gradient = analytic;
     data.gradient_step = kGradientStep;
     for (size_t i = 0; i < freezed_dofs_.size(); ++i) if (!freezed_dofs_[i]) data.free_indices.push_back(static_cast<int>(i));
     const unsigned M = static_cast<unsigned>(data.free_indices.size());
@@ -215,6 +282,31 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     for (double& d : step) d *= initial_step_scale;
     api.set_initial_step(solver, step.data());
 
+    // Batched start: BOBYQA's first 2M+1 interpolation points in one GPU batch; the callback then serves
+    // them from the cache (bitwise match on x) while the solver walks through its serial initialisation.
+    data.start_cache_x.clear(); data.start_cache_f.clear(); data.start_cache_hits = 0;
+    if (!cancelled && !want_gradient && batched_start_ && std::string(algorithm) == "LN_BOBYQA") {
+        const std::vector<VecN> pts = PredictBobyqaStart(x_star, l, u, step);
+        if (!pts.empty()) {
+            std::vector<double> X(pts.size() * x_initial.size());
+            for (size_t b = 0; b < pts.size(); ++b) {
+                const VecN full = rev(pts[b]);
+                std::copy(full.begin(), full.end(), X.begin() + b * x_initial.size());
+            }
+            std::vector<double> fb(pts.size());
+            {
+                std::lock_guard<std::recursive_mutex> eg(engine_mutex_);
+                // the scene-specialised kernel, as for the single evaluations it stands in for: bit-identical values
+                omo_set_batch_hint(Engine(), 1 << 30);
+                try { CalculateFullObjectiveBatch(data.min_t, data.max_t, X.data(), static_cast<int>(pts.size()), x_original, fb.data()); }
+                catch (...) { omo_set_batch_hint(Engine(), 0); throw; }
+                omo_set_batch_hint(Engine(), 0);
+            }
+            data.start_cache_x = pts;
+            data.start_cache_f = fb;
+        }
+    }
+
     const auto t_start = std::chrono::steady_clock::now();
     double final_cost_value = initial_cost_value;
     int result = 0;
@@ -229,6 +321,7 @@ void Core::Solve(bool explicit_termination, const char* algorithm, bool want_gra
     if (result < 0 && result != -4 && result != -5) x_star = sel(x_initial);
     last_solve_value_ = final_cost_value;
     last_solve_evals_ = numevals;
+    last_solve_batched_ = data.start_cache_hits;
     last_solve_status_ = cancelled ? "forced_stop" : std::to_string(result);
 
     const double ms = std::chrono::duration<double, std::milli>(t_end - t_start).count();

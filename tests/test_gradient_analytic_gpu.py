@@ -54,26 +54,24 @@ def test_analytic_gradient_matches_the_finite_difference_gradient(oracle_port, n
 
 def test_analytic_gradient_with_free_times_and_values():
     """t and v of the control points freed as well (the reference's default freezes them, core.cpp:83-88): the derivative with
-    respect to a key time goes through the implicit root of BOTH adjacent segments."""
+    respect to a key time goes through the implicit root of BOTH adjacent segments. f is only piecewise smooth in a key time -- a
+    key that crosses a sample time switches that sample's segment -- and the shipped keys sit on whole frames, i.e. exactly ON
+    sample times, where a central difference straddles the kink. The keys are therefore moved 0.05 frames off the sample grid
+    (samples are 0.2 apart, h = 1e-4): there the difference quotient is a fair reference for every field."""
     c = Core(scene_path("stick-figure"))
     x0 = c.GetDescriptor()
     c.freezed_dofs_ = np.zeros(x0.size, dtype=np.int32)
     x = synthetic.perturbed_candidates(x0, 1, first=2)[0]
+    x[0::5] += 0.05
     lo, hi = c.window
     f_an, g_an, used = c.CalculateAnalyticGradient(lo, hi, x, x0)
     f_fd, g_fd, _ = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
     assert used and g_an.size == x0.size
-    # values, tangents and handle lengths: smooth, compared entry by entry
+    scale = max(float(np.max(np.abs(g_fd))), 1.0)
+    assert np.max(np.abs(g_an - g_fd)) <= 2e-6 * scale, np.max(np.abs(g_an - g_fd)) / scale
     field = np.arange(x0.size) % 5
-    scale = max(float(np.max(np.abs(g_fd[field != 0]))), 1.0)
-    assert np.max(np.abs(g_an[field != 0] - g_fd[field != 0])) <= 2e-6 * scale
-    # key times: one that crosses a sample time switches that sample's segment -- f is only piecewise smooth in t, and the shipped
-    # keys sit on whole frames, i.e. exactly ON sample times. The central difference is meaningful where its one-sided halves agree.
-    _, _, fpm = c.CalculateGradient(lo, hi, x, x0, h=1e-4)
-    fwd, bwd = (fpm[:, 0] - f_fd) / 1e-4, (f_fd - fpm[:, 1]) / 1e-4
-    ok = (field == 0) & (np.abs(fwd - bwd) <= 1e-2 * np.maximum(np.abs(g_fd), 1.0))
-    assert ok.sum() >= 5
-    assert np.max(np.abs(g_an[ok] - g_fd[ok])) <= 1e-4 * max(float(np.max(np.abs(g_fd[ok]))), 1.0)
+    for k in range(5):
+        assert np.max(np.abs(g_an[field == k])) > 0
 
 
 def test_scenes_outside_the_analytic_gradient_fall_back_to_finite_differences():

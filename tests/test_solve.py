@@ -128,3 +128,58 @@ def test_fox_tail_gradient_based_solve(oracle_port, algorithm):
     assert (x_after[:, 3] < 0).all() and (x_after[:, 4] > 0).all()
     with pytest.raises(Exception):
         c.PerformOptimizationWithGradient(False, "LN_BOBYQA")
+
+
+@needs_nlopt
+@pytest.mark.gpu
+def test_fox_tail_solve_over_the_analytic_gradient(oracle_port):
+    """Next row N4 in the solver: LD_SLSQP driven by omo_eval_grad_analytic reaches the optimum of the finite-difference-driven
+    solve (same bounds, same tolerances) -- and every callback's f is the reference objective."""
+    from optimo_b200.core import Core
+
+    def run(analytic):
+        c = Core(scene_path("fox-tail"))
+        c.select_items(["tail_root", "tail_center"])
+        c.record_solve_trace(True)
+        f, evals = c.PerformOptimizationWithGradient(False, "LD_SLSQP", analytic=analytic)
+        return c, f, evals
+    c_fd, f_fd, n_fd = run(False)
+    c_an, f_an, n_an = run(True)
+    assert abs(f_an - f_fd) <= 1e-4 * abs(f_fd), (f_an, f_fd)
+    assert n_an <= 2 * n_fd
+    X, F = c_an.solve_trace()
+    o = oracle_port.Oracle(scene_path("fox-tail"), "port"); o.set_sampling_concurrency(1)
+    o.select_items(["tail_root", "tail_center"])
+    x0 = o.descriptor()
+    idx = o.free_indices()
+    x_init, _, _ = nlopt_driver.bounds_like_perform_optimization(x0)
+    for k in range(0, X.shape[0], 7):
+        full = x_init.copy(); full[idx] = X[k]
+        fo, _ = o.full_objective(full, x0)
+        assert abs(F[k] - fo) <= 1e-9 * abs(fo)
+
+
+@needs_nlopt
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,items", [("fox-tail", ["tail_root", "tail_center"]), ("stick-figure", None)])
+def test_batched_bobyqa_start_leaves_the_iterates_unchanged(name, items):
+    """SURVEY.md section 8(f) N1, second half: BOBYQA's first 2M+1 interpolation points (bobyqa.c prelim_: x0 and x0 +- rho e_i, shifted at
+    bounds, in NLopt's rescaled variables) are predicted bit for bit, evaluated as one batch and served from a cache. Every one of
+    them must be hit, and the solve must ask the same questions and get the same answers as the serial start."""
+    from optimo_b200.core import Core
+
+    def run(batched):
+        c = Core(scene_path(name))
+        if items:
+            c.select_items(items)
+        c.set_batched_start(batched)
+        c.record_solve_trace(True)
+        f, evals = c.PerformOptimization(False)
+        X, F = c.solve_trace()
+        return f, evals, X, F, c.last_solve_batched, c.free_indices().size
+
+    f0, e0, X0, F0, h0, M = run(False)
+    f1, e1, X1, F1, h1, _ = run(True)
+    assert h0 == 0 and h1 == 2 * M + 1, (h1, M)
+    assert (f0, e0) == (f1, e1)
+    assert np.array_equal(X0, X1) and np.array_equal(F0, F1)
