@@ -438,6 +438,17 @@ def measure_single(G, W, steps, warmup, dfma_peak, cpu_candidates, full=False, s
         assert rel <= 1e-9, f"{W.name}: GPU deviates from the CPU reference: {rel}"
         out["max_rel_diff_vs_oracle"] = rel
         out["oracle"] = {"kind": leg["kind"], "rows_compared": int(rows.shape[0]), "cpu_value": rows.shape[0] * leg["n_s"] / leg["seconds"], "cpu_cores": leg["cores"]}
+        if W.grad and not W.core.item_names()[-1].endswith("IK"):
+            # next row N4: the analytic gradient of the same point, timed through the Core API (host x in, gradient out)
+            t_an = []
+            for rep in range(8):
+                t0 = time.perf_counter()
+                f_an, g_an, used = W.core.CalculateAnalyticGradient(W.lo, W.hi, W.x_base, W.x0)
+                t_an.append(time.perf_counter() - t0)
+            g_fd_gpu = grad_out["g"]
+            out["analytic_gradient"] = {"used": bool(used), "us_per_call": float(np.median(t_an[2:]) * 1e6),
+                                        "max_abs_diff_vs_fd_gradient": float(np.max(np.abs(g_an - g_fd_gpu))), "g_inf": float(np.max(np.abs(g_fd_gpu))),
+                                        "api": "omo_eval_grad_analytic through Core::CalculateFullObjectiveAndAnalyticGradient (wall clock)"}
         if W.grad:
             F = W.idx.size
             g_ref = (leg["f"][1::2] - leg["f"][2::2]) / (2.0 * H)
@@ -486,7 +497,7 @@ def measure_solve(G, dfma_peak):
            "max_rel_diff_vs_oracle": rel, "oracle": {"kind": "reference" if kind == "ref" else "port", "rows_compared": int(rows.shape[0])},
            "cpu_us_per_callback_as_is": sec_serial / n_cpu * 1e6, "roofline_frac": None,
            "roofline_note": "latency-bound: one candidate x 245 samples per launch (2 thread blocks); frac is not meaningful",
-           "graph_replays": c.engine().graph_replays()}
+           "graph_replays": c.engine().graph_replays(), "callbacks_served_by_the_batched_start": c.last_solve_batched}
     # next row N1: the gradient-based solve over the finite-difference gradient
     c.SetDescriptor(x_init)
     c.PerformOptimizationWithGradient(False, "LD_SLSQP")
@@ -494,6 +505,12 @@ def measure_solve(G, dfma_peak):
     t0 = time.perf_counter()
     fg, eg = c.PerformOptimizationWithGradient(False, "LD_SLSQP")
     out["gradient_solve"] = {"algorithm": "LD_SLSQP", "ms": (time.perf_counter() - t0) * 1e3, "callbacks": int(eg), "f_final": float(fg)}
+    c.SetDescriptor(x_init)
+    c.PerformOptimizationWithGradient(False, "LD_SLSQP", analytic=True)
+    c.SetDescriptor(x_init)
+    t0 = time.perf_counter()
+    fa, ea = c.PerformOptimizationWithGradient(False, "LD_SLSQP", analytic=True)
+    out["analytic_gradient_solve"] = {"algorithm": "LD_SLSQP", "ms": (time.perf_counter() - t0) * 1e3, "callbacks": int(ea), "f_final": float(fa)}
     return out
 
 
