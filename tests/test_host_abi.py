@@ -165,3 +165,22 @@ def test_history_stack_and_files_need_no_gpu(tmp_path):
     assert c.GetHistorySize() == 0
     with pytest.raises(EngineError):
         c.CalculateTorques(3.0)       # the torque query itself is GPU work: no fallback
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_write_json_is_byte_for_byte_what_json11_writes(name):
+    """Core::WriteJson / ConvertCurrentSceneToJson (core_io.cpp:165-169,216-226) against goldens written by the reference's OWN json11
+    (oracle/json11_writer.cpp restates core_io.cpp's Json construction over external/json11/json11.cpp, compiled where it lies;
+    tests/golden/json11_scene_*.txt). With awkward doubles too, through the helper's canonical form when it is built."""
+    import subprocess
+    c = Core(scene_path(name))
+    golden = open(os.path.join(ROOT, "tests", "golden", f"json11_scene_{name}.txt")).read()
+    assert c.scene_json() == golden
+    helper = os.path.join(ROOT, "oracle", "_ref", "json11_writer")
+    if os.path.exists(helper):
+        x = c.GetDescriptor()
+        rng = np.random.default_rng(4)
+        c.SetDescriptor(x * (1.0 + 1e-3 * rng.standard_normal(x.size)) + 1e-7 * rng.standard_normal(x.size) + np.pi * 1e5 * (rng.random(x.size) < 0.05))
+        text = c.scene_json()
+        canon = subprocess.run([helper, "canon"], input=text.encode(), capture_output=True, check=True).stdout.decode()
+        assert text == canon

@@ -108,3 +108,19 @@ def test_export_motion_and_history_files(name, tmp_path, oracle_port):
     # the engine follows the undone scene
     tau = c.CalculateTorques(10.0)
     assert rel_err(tau, o.torques_at(x, [10.0])["tau"][0]) <= _tol(name)
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_export_motion_text_is_json11_canonical(name):
+    """Core::ExportMotion (core_io.cpp:252-294) writes json11's dump of every frame. The product's text, parsed and dumped again by
+    the reference's own json11 (oracle/_ref/json11_writer canon), must come back byte for byte: key order, separators, %.17g."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    helper = os.path.join(ROOT, "oracle", "_ref", "json11_writer")
+    if not os.path.exists(helper):
+        pytest.skip("oracle/_ref/json11_writer not built (make -C oracle ref, needs /root/reference)")
+    c = Core(scene_path(name))
+    text = c.motion_json()
+    canon = subprocess.run([helper, "canon"], input=text.encode(), capture_output=True, check=True).stdout.decode()
+    assert text == canon and text.startswith('[{"frame": ')
