@@ -1206,7 +1206,9 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
     if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
     const size_t bytes = (size_t)B * ctx->D * sizeof(double);
     if (ctx->graph_mode < 0) { const char* e = std::getenv("OMO_GRAPH"); ctx->graph_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
-    if (B == 1 && self_usable(ctx)) {
+    // (a context that evaluates ONE row of a larger batch -- a device of omo_multi -- stays on the batch kernels: same bits as the whole batch)
+    const bool lone = B == 1 && ctx->batch_hint <= 1;
+    if (lone && self_usable(ctx)) {
         // one launch: x travels as a kernel parameter, the kernel prepares, evaluates, reduces and writes (f, C, D_param, D_traj)
         // into mapped host memory
         if ((st = ensure_self_buffers(ctx, 1)) != OMO_OK) return st;
@@ -1219,7 +1221,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
             return OMO_OK;
         }
     }
-    if (B == 1 && ctx->graph_mode == 1 && !ctx->timing) {
+    if (lone && ctx->graph_mode == 1 && !ctx->timing) {
         // The solver's callback: one candidate per call, thousands of calls. The first call with a given state runs the plain
         // path below (it finishes every lazy allocation / module load), the second captures, the rest replay.
         if (!ctx->h_single) OMO_CUDA(cudaHostAlloc((void**)&ctx->h_single, (size_t)(ctx->D + 4) * sizeof(double), cudaHostAllocDefault));
