@@ -64,9 +64,9 @@ __device__ __forceinline__ void walk_loop(W& w, const short* __restrict__ place)
             const int g0 = S.grp_begin[grp], g1 = S.grp_begin[grp + 1];
             if (grp + 1 < S.n_groups) w.stage_issue((grp + 1) & 1, g1, S.grp_begin[grp + 2] - g1);
             const int n3 = (g1 - g0) / 3, rem = (g1 - g0) - 3 * n3;
-            w.template curve_group<0>(grp & 1, g0, n3);
-            if (rem == 1) w.template curve_staged<1>(grp & 1, g0 + 3 * n3, 3 * n3, S.grp_list[g0 + 3 * n3], -1, -1);
-            else if (rem == 2) w.template curve_staged<2>(grp & 1, g0 + 3 * n3, 3 * n3, S.grp_list[g0 + 3 * n3], S.grp_list[g0 + 3 * n3 + 1], -1);
+            if (rem == 0) w.template curve_group<0>(grp & 1, g0, n3);
+            else if (rem == 1) w.template curve_group<1>(grp & 1, g0, n3);
+            else w.template curve_group<2>(grp & 1, g0, n3);
             w.stage_wait();
             w.group_sync();
         }

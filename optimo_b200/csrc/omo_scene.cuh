@@ -119,6 +119,13 @@ struct OmoEvalParams {
     int triplet;
     int n_smem_slots;  // deep-tree instance of the table-driven kernel: stack slots held in shared memory, the rest per thread
     double* o_root;
+    // ---- sorted curve work lists (scene-specialised batch kernels) ------------------------------------------------------------
+    // perm[tile][perm_stride]: for every curve group, its (local channel << 7 | sample slot) items of the tile's 128-sample window
+    // sorted by the Newton iteration count the ORIGINAL motion needs there (descending; 0xFFFF pads a group to whole triples).
+    // A warp's lockstep solve then runs curves of similar cost together instead of waiting for its slowest lane
+    // (omo_walk.cuh: curve_group). null: every lane solves the curves of its own sample.
+    const unsigned short* perm;
+    int perm_stride;
     // ---- self-preparing instances (Walker SELF; single candidates and small finite-difference gradients) --------------------
     // One launch does what the batch path spreads over perturb_kernel -> prepare_kernel -> objective -> finish_kernel and two
     // copies: the base descriptor x arrives as a KERNEL PARAMETER (constant bank), every block prepares its row's control

@@ -76,6 +76,9 @@ struct Walker {
     const double* __restrict__ sgc;   // SEGG > 0: this candidate's segment records
     double* wsb;                      //           staging buffers [buf][SEGG][OMO_SEGW][OMO_SEGD]
     int* wbase;                       //           [n_keyed] chain position of each keyed channel's first staged record
+    int *wcn, *wrow;                  //           [n_keyed] control points / exchange row of each keyed channel (sorted work lists: per-lane lookups)
+    double* wts;                      //           [NT] the sample times of the block's window
+    int perm_cursor;                  //           entries of the tile's sorted list consumed by the groups solved so far
     const unsigned short* __restrict__ tsg;   //   this (candidate, tile)'s row of the tile table
     const double* xs;                 // SELF: the base descriptor (kernel parameter, constant bank)
     double* seg_sm;                   //       this row's segment records [n_cp + OMO_SEGW][OMO_SEGD] in shared memory
@@ -161,15 +164,23 @@ struct Walker {
             seg0 = nullptr;
             sgc = P.seg + (size_t)cand * P.n_cp * OMO_SEGD;
             double* tail = stk0 + (size_t)n_smem_slots * ((CPT ? 1 : OMO_SLOT) * NT);
-            const int wb_doubles = ((S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double);
-            if (!stage_in_stack) { wbase = reinterpret_cast<int*>(tail); wsb = tail + wb_doubles; }
-            else { wbase = reinterpret_cast<int*>(stk0); wsb = stk0 + wb_doubles; }
+            // [wbase | wcn | wrow : n_keyed ints each][wts : NT doubles][staging buffers]
+            const int wb_doubles = ((3 * S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double) + NT;
+            double* const area = stage_in_stack ? stk0 : tail;
+            wbase = reinterpret_cast<int*>(area); wcn = wbase + S.n_keyed; wrow = wcn + S.n_keyed;
+            wts = area + (wb_doubles - NT);
+            wsb = area + wb_doubles;
+            perm_cursor = 0;
             // wbase[] is published by the barrier that follows the first stage_issue / stage_wait; that first stage reads
             // the tile table itself, so the block start is two dependent global round trips deep, not three
             tsg = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
             if (sorted) {
 #pragma unroll 1
-                for (int i = tid; i < S.n_keyed; i += NT) wbase[i] = stage_base(i);
+                for (int i = tid; i < S.n_keyed; i += NT) {
+                    wbase[i] = stage_base(i);
+                    const int ch = S.grp_list[i];
+                    wcn[i] = S.chan_n[ch]; wrow[i] = S.chan_row[ch];
+                }
             }
         } else {
         // seg0[warp][n_keyed] (16-bit) sits behind the stack in dynamic shared memory
@@ -199,6 +210,7 @@ struct Walker {
         owned = (idx >= 2) && (s_raw < tile_end) && (s_raw >= 0) && item_valid;
         interior = (s >= 2) && (s <= N - 3) && !(OUT && P.triplet != 0);
         t = __ldg(P.tgrid + s);
+        if (SEGG > 0 && !SELF) wts[idx] = t;           // published by the barrier that follows the first stage
         tsq = (!OUT && interior) ? S.static_tsq : 0.0;   // the pruned bodies' share (candidate-independent)
         dtr = 0.0;
         set_root();
@@ -529,7 +541,10 @@ struct Walker {
                 base[k] = wbase[i0 + k];
             }
             unsigned fb = 0, eb = 0, en = 0;
-            eval_channels_staged<K, COUNT>(sk, nn, base, t, val, fb, eb, en);
+            double tk[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) tk[k] = t;
+            eval_channels_staged<K, COUNT>(sk, nn, base, tk, val, fb, eb, en);
             if (fb) {   // this thread's segment lies beyond the staged window (keys denser than OMO_SEGW per block)
 #pragma unroll
                 for (int k = 0; k < K; ++k)
@@ -619,10 +634,59 @@ struct Walker {
     // A whole curve group: n3 lockstep triples as ONE loop body (the channel numbers come from grp_list) plus a tail of
     // `rem` curves. Keeps the code of a 189-curve scene the size of one triple -- the specialised kernel is bound by
     // instruction supply (profiles/micro/icache_mix), straight-line repetition of the solver is what it cannot afford.
+    // Sorted form of a curve group (OmoEvalParams::perm): the group's (channel, sample) items of this tile come in the order of
+    // the Newton iterations the ORIGINAL motion needs for them; chunk p of 96 items is solved by warp p % 4 as one lockstep triple
+    // (32 lanes x 3 curves), so curves of similar cost share a warp instead of every warp waiting for the slowest of its 96. Which
+    // lane solves which curve changes nothing in the curve's own arithmetic: the exchange rows hold the same bits.
+    __device__ __forceinline__ void curve_group_sorted(const int buf, const int g0, const int n3tot)
+    {
+        const OmoDevScene& S = c_scene;
+        const unsigned short* __restrict__ list = P.perm + (size_t)tile_ * P.perm_stride + perm_cursor + ((tid >> 5) * 3) * 32 + (tid & 31);
+        perm_cursor += n3tot * 3 * NT;
+        unsigned e0 = __ldg(list), e1 = __ldg(list + 32), e2 = __ldg(list + 64);
+#pragma unroll 1
+        for (int c = 0; c < n3tot; ++c) {
+            const unsigned e[3] = {e0, e1, e2};
+            if (c + 1 < n3tot) {   // next triple's items travel while this one is solved
+                const unsigned short* __restrict__ nx = list + (size_t)(c + 1) * (3 * NT);
+                e0 = __ldg(nx); e1 = __ldg(nx + 32); e2 = __ldg(nx + 64);
+            }
+            const double* sk[3];
+            int nn[3], base[3], si[3], lc[3];
+            double tk[3], val[3];
+            bool on[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                on[k] = e[k] != 0xffffu;
+                lc[k] = on[k] ? (int)(e[k] >> 7) : 0;
+                si[k] = (int)(e[k] & 127u);
+                sk[k] = wsb + (size_t)((buf * SEGG + lc[k]) * OMO_SEGW) * OMO_SEGD;
+                nn[k] = on[k] ? wcn[g0 + lc[k]] : 0;
+                base[k] = wbase[g0 + lc[k]];
+                tk[k] = wts[si[k]];
+            }
+            unsigned fb = 0, eb = 0, en = 0;
+            eval_channels_staged<3, COUNT>(sk, nn, base, tk, val, fb, eb, en);
+            if (fb) {   // the item's segment lies beyond the staged window (keys denser than OMO_SEGW per block)
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    if (on[k] && (fb >> k & 1u)) {
+                        const int ch = S.grp_list[g0 + lc[k]];
+                        val[k] = COUNT ? eval_channel(pc, P.n_cp, S.chan_pos[ch], nn[k], tk[k], true, eb, en)
+                                       : eval_channel_slow(pc, P.n_cp, S.chan_pos[ch], nn[k], tk[k], true);
+                    }
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                if (on[k]) ex[wrow[g0 + lc[k]] * NT + si[k]] = val[k];
+        }
+    }
+
     template <int REM>
     __device__ __forceinline__ void curve_group(const int buf, const int g0, const int n3)
     {
         const OmoDevScene& S = c_scene;
+        if (SEGG > 0 && !SELF && !COUNT && P.perm != nullptr && sorted) { curve_group_sorted(buf, g0, n3 + (REM > 0 ? 1 : 0)); return; }
 #pragma unroll 1
         for (int c = 0; c < n3; ++c) {
             const int i0 = g0 + 3 * c;

@@ -604,3 +604,27 @@ def test_one_launch_path_is_bit_identical_to_the_general_path(monkeypatch, name)
         assert np.array_equal(a[3], b[3]) and np.array_equal(a[4], b[4])
         assert a[0] == a[2]                          # f of the single call == f0 of the gradient call
     assert res["1"][1] > 0
+
+
+@pytest.mark.parametrize("name", ["stick240", "tree24"])
+def test_sorted_curve_work_lists_change_no_bit(monkeypatch, name):
+    """Large launches of the scene-specialised kernel solve each tile's (channel, sample) curve items in the order of the Newton
+    iterations x_original's motion needs for them (OmoEvalParams::perm, omo.cu: build_perm), so that a warp's lockstep triple holds
+    curves of similar cost. Which lane solves which curve must not change a bit of any value -- against the per-sample order
+    (OMO_SORTED_CURVES=0), with an x_original that is then replaced, a candidate with an unsorted chain in the batch, and w_traj."""
+    scene = synthetic.stick_240(load_scene("stick-figure")) if name == "stick240" else synthetic.tree_scene(n_joints=24, n_frames=400)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("OMO_SORTED_CURVES", mode)
+        c = Core(scene)
+        x0 = c.GetDescriptor()
+        lo, hi = c.window
+        B = 1200 if name == "stick240" else 400
+        X = synthetic.perturbed_candidates(x0, B)
+        X[7, 0] = X[7, 5] + 0.25                       # one candidate's first chain becomes unsorted
+        out = [c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True)]
+        c.UpdateGlobalWeight(2.5)
+        out.append(c.CalculateFullObjectiveBatch(lo, hi, X, X[3], want_terms=True))     # another x_original: the lists are rebuilt
+        res[mode] = out
+    for a, b in zip(res["0"], res["1"]):
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
