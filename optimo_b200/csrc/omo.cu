@@ -40,6 +40,9 @@ struct omo_ctx {
     int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;      // host -> device copies of omo_eval, pipelined against the kernels on `stream`
+    cudaStream_t stream2 = nullptr;          // second compute stream: odd chunks of a pipelined batch, so that the partial last wave of chunk i
+                                             // overlaps the first waves of chunk i+1 (a chunk's launches lose most of a wave otherwise)
+    cudaEvent_t join_ev = nullptr, fork_ev = nullptr;
     cudaEvent_t chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t done_ev = nullptr;
     std::string err;
@@ -101,6 +104,8 @@ struct omo_ctx {
 
     // work buffers (capacity in candidates)
     int cap = 0, cap_tiles = 0;   // candidates / tiles per candidate the work buffers were sized for
+    int row0 = 0;                 // first scratch row of the launches being queued (a chunk of a pipelined batch works in its own rows, so that
+                                  // chunks may run on two streams at once)
     double *d_X = nullptr, *d_prep = nullptr, *d_dparam = nullptr, *d_partial = nullptr, *d_f = nullptr, *d_terms = nullptr;
     unsigned* d_flags = nullptr;
     double* d_seg = nullptr;              // [cap][n_cp][OMO_SEGD] prepared segments
@@ -434,7 +439,16 @@ omo_status activate_scene(omo_ctx* ctx)
 
 // prepare_kernel's split of a candidate's chain positions over blocks
 constexpr int kPrepChunk = 640;
-int prep_parts(const omo_ctx* ctx) { return std::max(1, (ctx->n_cp + kPrepChunk - 1) / kPrepChunk); }
+int prep_parts(const omo_ctx* ctx) { return std::max(1, (ctx->n_cp + 640 - 1) / 640); }
+
+// scratch of the candidate rows [row0, row0 + B) of the launches being queued
+double* sc_prep(const omo_ctx* c) { return c->d_prep + (size_t)c->row0 * 6 * c->n_cp; }
+unsigned* sc_flags(const omo_ctx* c) { return c->d_flags + c->row0; }
+double* sc_seg(const omo_ctx* c) { return c->d_seg + (size_t)c->row0 * c->n_cp * OMO_SEGD; }
+unsigned short* sc_tile_seg(const omo_ctx* c) { return c->d_tile_seg + (size_t)c->row0 * std::max(c->n_tiles, 1) * std::max(c->hs.n_keyed, 1); }
+double* sc_partial(const omo_ctx* c) { return c->d_partial + (size_t)c->row0 * std::max(c->n_tiles, 1) * 2; }
+int prep_parts(const omo_ctx* ctx);
+double* sc_dparam(const omo_ctx* c) { return c->d_dparam + (size_t)c->row0 * prep_parts(c); }
 
 omo_status ensure_capacity(omo_ctx* ctx, int B)
 {
@@ -633,7 +647,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
             if (d_item_map) return OMO_OK;
-            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
+            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
             OMO_CUDA(cudaGetLastError());
             ctx->launches += 1;
             return OMO_OK;
@@ -651,7 +665,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
     if (st != OMO_OK) return st;
     if (d_item_map) return OMO_OK;
-    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_partial, ctx->d_dparam, B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
+    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return OMO_OK;
@@ -660,7 +674,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
 void fill_params(const omo_ctx* ctx, OmoEvalParams& P)
 {
     std::memset(&P, 0, sizeof(P));
-    P.prep = ctx->d_prep; P.flags = ctx->d_flags; P.seg = ctx->d_seg; P.tile_seg = ctx->d_tile_seg; P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = ctx->d_partial;
+    P.prep = sc_prep(ctx); P.flags = sc_flags(ctx); P.seg = sc_seg(ctx); P.tile_seg = sc_tile_seg(ctx); P.tgrid = ctx->d_tgrid; P.wcost = ctx->d_wcost; P.partial = sc_partial(ctx);
     P.N_s = ctx->N_s; P.n_cp = ctx->n_cp;
     const double dt = ctx->dt;
     P.dt = dt; P.inv_dt = 1.0 / dt; P.inv_2dt = 1.0 / (2.0 * dt); P.inv_12dt = 1.0 / (12.0 * dt);
@@ -676,14 +690,14 @@ omo_status run_prepare(omo_ctx* ctx, const double* dX, int B)
     omo::OmoPrepParams Q;
     Q.X = dX; Q.x0 = ctx->d_x0; Q.wparam = ctx->d_wparam;
     Q.cp_of_pos = ctx->d_cp_of_pos; Q.first_of_pos = ctx->d_first_of_pos; Q.last_of_pos = ctx->d_last_of_pos; Q.next_same = ctx->d_next_same;
-    Q.prep = ctx->d_prep; Q.flags = ctx->d_flags; Q.dparam = ctx->d_dparam;
+    Q.prep = sc_prep(ctx); Q.flags = sc_flags(ctx); Q.dparam = sc_dparam(ctx);
     Q.n_cp = ctx->n_cp; Q.D = ctx->D; Q.cyclic = ctx->cyclic;
-    Q.seg = ctx->d_seg; Q.tile_seg = ctx->d_tile_seg; Q.tgrid = ctx->d_tgrid;
+    Q.seg = sc_seg(ctx); Q.tile_seg = sc_tile_seg(ctx); Q.tgrid = ctx->d_tgrid;
     Q.N_s = ctx->N_s; Q.T_out = ctx->T_out; Q.n_tiles = ctx->n_tiles; Q.n_keyed = ctx->hs.n_keyed;
     Q.chunk = std::min(kPrepChunk, std::max(ctx->n_cp, 1));
     const size_t sh = (size_t)6 * (Q.chunk + 1) * sizeof(double);
     // bit 0 of every flag word = "sorted": preset here when several blocks share a candidate, written by the one block otherwise
-    if (prep_parts(ctx) > 1) OMO_CUDA(cudaMemsetAsync(ctx->d_flags, 1, (size_t)B * sizeof(unsigned), ctx->stream));
+    if (prep_parts(ctx) > 1) OMO_CUDA(cudaMemsetAsync(sc_flags(ctx), 1, (size_t)B * sizeof(unsigned), ctx->stream));
     omo::prepare_kernel<<<dim3((unsigned)B, (unsigned)prep_parts(ctx)), 128, sh, ctx->stream>>>(Q);
     OMO_CUDA(cudaGetLastError());
     ctx->launches += 1;
@@ -1078,11 +1092,35 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
             OMO_CUDA(cudaMemcpyAsync(d_stage + (size_t)b0 * W, X + (size_t)b0 * W, (size_t)nb * W * sizeof(double), cudaMemcpyHostToDevice, ctx->copy_stream));
             OMO_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
         }
+        // chunks alternate between two compute streams (their scratch rows are disjoint); everything joins on `stream` again
+        const bool two = std::getenv("OMO_EVAL_ONE_STREAM") == nullptr;
+        if (two && !ctx->stream2) {
+            OMO_CUDA(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+            OMO_CUDA(cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming));
+            OMO_CUDA(cudaEventCreateWithFlags(&ctx->fork_ev, cudaEventDisableTiming));
+        }
+        cudaStream_t const main_stream = ctx->stream;
+        if (two) {   // stream2 starts after whatever `stream` has queued so far (uploads of tables, earlier calls)
+            OMO_CUDA(cudaEventRecord(ctx->fork_ev, main_stream));
+            OMO_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->fork_ev, 0));
+        }
+        bool used2 = false;
         for (int c = 0; c < n_chunks; ++c) {
             const int b0 = bound[c], nb = bound[c + 1] - b0;
             if (nb <= 0) continue;
-            OMO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0));
-            if ((st = evaluate(b0, nb)) != OMO_OK) return st;
+            const bool odd = two && (c & 1);
+            if (odd) { ctx->stream = ctx->stream2; used2 = true; }
+            ctx->row0 = b0;     // this chunk's own scratch rows
+            cudaError_t we = cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[c], 0);
+            st = we == cudaSuccess ? evaluate(b0, nb) : OMO_CUDA_ERROR;
+            ctx->stream = main_stream;
+            ctx->row0 = 0;
+            if (we != cudaSuccess) return fail(ctx, OMO_CUDA_ERROR, cudaGetErrorString(we));
+            if (st != OMO_OK) return st;
+        }
+        if (used2) {
+            OMO_CUDA(cudaEventRecord(ctx->join_ev, ctx->stream2));
+            OMO_CUDA(cudaStreamWaitEvent(main_stream, ctx->join_ev, 0));
         }
     }
     if (d_f_dst) return OMO_OK;
@@ -1157,6 +1195,9 @@ void omo_destroy(omo_ctx* ctx)
     for (auto& e : ctx->chunk_ev) if (e) cudaEventDestroy(e);
     if (ctx->done_ev) cudaEventDestroy(ctx->done_ev);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->join_ev) cudaEventDestroy(ctx->join_ev);
+    if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
