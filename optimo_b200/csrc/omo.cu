@@ -642,7 +642,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
         P.perm = ctx->perm_valid ? ctx->d_perm : nullptr;
         P.perm_stride = ctx->perm_stride;
     }
-    if ((long long)P.n_items < 4096) P.perm = nullptr;
+    if ((long long)P.n_items < 4096 || count || out) P.perm = nullptr;
     if (!out && mode != 0 && (mode == 1 || d_item_map != nullptr || ctx->prefer_jit || sized_as * plan.t_out >= 65536)) {
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
@@ -808,7 +808,12 @@ omo_status build_perm(omo_ctx* ctx)
                     items.emplace_back(-(int)cnt[(size_t)(g0 + lc) * N + s], (unsigned short)((lc << 7) | si));
                 }
             std::stable_sort(items.begin(), items.end(), [](const std::pair<int, unsigned short>& p, const std::pair<int, unsigned short>& q) { return p.first < q.first; });
-            for (size_t k = 0; k < items.size(); ++k) perm[off + k] = items[k].second;
+            // chunk q of 96 sorted items goes to triple q / 4 of warp q % 4 -- in snake order (odd rows reversed), so that the four warps
+            // of the block carry equal shares of the expensive curves and meet at the group's barrier together
+            for (size_t k = 0; k < items.size(); ++k) {
+                const size_t q = k / 96, row = q / 4, w = (row & 1) ? 3 - (q % 4) : (q % 4);
+                perm[off + (row * 4 + w) * 96 + (k % 96)] = items[k].second;
+            }
             off += (size_t)((ng + 2) / 3) * 3 * kBlockThreads;
         }
     }

@@ -79,6 +79,8 @@ struct Walker {
     int *wcn, *wrow;                  //           [n_keyed] control points / exchange row of each keyed channel (sorted work lists: per-lane lookups)
     double* wts;                      //           [NT] the sample times of the block's window
     int perm_cursor;                  //           entries of the tile's sorted list consumed by the groups solved so far
+    int perm_staged;                  //           ... and staged so far (the list of a group travels with its segment records)
+    unsigned short* wpm;              //           staged slices of the sorted list, [buf][ceil(SEGG / 3) * 3 * NT]
     const unsigned short* __restrict__ tsg;   //   this (candidate, tile)'s row of the tile table
     const double* xs;                 // SELF: the base descriptor (kernel parameter, constant bank)
     double* seg_sm;                   //       this row's segment records [n_cp + OMO_SEGW][OMO_SEGD] in shared memory
@@ -170,7 +172,8 @@ struct Walker {
             wbase = reinterpret_cast<int*>(area); wcn = wbase + S.n_keyed; wrow = wcn + S.n_keyed;
             wts = area + (wb_doubles - NT);
             wsb = area + wb_doubles;
-            perm_cursor = 0;
+            wpm = reinterpret_cast<unsigned short*>(wsb + (size_t)(S.n_groups > 1 ? 2 : 1) * SEGG * OMO_SEGW * OMO_SEGD);
+            perm_cursor = 0; perm_staged = 0;
             // wbase[] is published by the barrier that follows the first stage_issue / stage_wait; that first stage reads
             // the tile table itself, so the block start is two dependent global round trips deep, not three
             tsg = P.tile_seg + ((size_t)cand * P.n_tiles + tile) * S.n_keyed;
@@ -507,6 +510,16 @@ struct Walker {
                 asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
             }
         }
+        if (P.perm != nullptr) {   // this group's slice of the tile's sorted work list
+            constexpr int kPermBuf = ((SEGG + 2) / 3) * 3 * NT;
+            const int entries = ((nch + 2) / 3) * 3 * NT;
+            const unsigned short* src = P.perm + (size_t)tile_ * P.perm_stride + perm_staged;
+            for (int u = tid; u < entries / 8; u += NT) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(wpm + (size_t)buf * kPermBuf + 8 * u);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + 8 * u) : "memory");
+            }
+            perm_staged += entries;
+        }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     __device__ __forceinline__ void stage_wait()
@@ -641,16 +654,13 @@ struct Walker {
     __device__ __forceinline__ void curve_group_sorted(const int buf, const int g0, const int n3tot)
     {
         const OmoDevScene& S = c_scene;
-        const unsigned short* __restrict__ list = P.perm + (size_t)tile_ * P.perm_stride + perm_cursor + ((tid >> 5) * 3) * 32 + (tid & 31);
+        constexpr int kPermBuf = ((SEGG + 2) / 3) * 3 * NT;
+        const unsigned short* __restrict__ list = wpm + (size_t)buf * kPermBuf + ((tid >> 5) * 3) * 32 + (tid & 31);
         perm_cursor += n3tot * 3 * NT;
-        unsigned e0 = __ldg(list), e1 = __ldg(list + 32), e2 = __ldg(list + 64);
 #pragma unroll 1
         for (int c = 0; c < n3tot; ++c) {
-            const unsigned e[3] = {e0, e1, e2};
-            if (c + 1 < n3tot) {   // next triple's items travel while this one is solved
-                const unsigned short* __restrict__ nx = list + (size_t)(c + 1) * (3 * NT);
-                e0 = __ldg(nx); e1 = __ldg(nx + 32); e2 = __ldg(nx + 64);
-            }
+            const unsigned short* __restrict__ cur = list + (size_t)c * (3 * NT);
+            const unsigned e[3] = {cur[0], cur[32], cur[64]};
             const double* sk[3];
             int nn[3], base[3], si[3], lc[3];
             double tk[3], val[3];
