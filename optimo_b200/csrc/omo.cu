@@ -761,13 +761,13 @@ omo_status install_grid(omo_ctx* ctx, std::vector<double>& grid, double dt)
 // (profiles/newton_sim.py: 24 % fewer lockstep rounds on stick240, 20 % on the 64-joint tree). Correctness does not depend on it.
 omo_status build_perm(omo_ctx* ctx)
 {
-    if (ctx->perm_mode < 0) { const char* e = std::getenv("OMO_SORTED_CURVES"); ctx->perm_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
+    if (ctx->perm_mode < 0) ctx->perm_mode = omo_jit::sorted_lists_enabled(ctx->hs) ? 1 : 0;
     ctx->perm_dirty = false; ctx->perm_valid = false;
     const OmoDevScene& S = ctx->hs;
     const int nk = S.n_keyed, N = ctx->N_s, n_tiles = ctx->n_tiles, T_out = ctx->T_out;
     // Measured on B200: stick240 (one group of 6 curves) 0.927 -> 0.885 ms; the 64-joint tree (16 groups of 12: a 4 MB list, four
     // triples per group to amortise the per-lane lookups over) 14.9 -> 15.2 ms. Scenes with many curve groups keep the per-sample order.
-    if (ctx->perm_mode != 1 || nk == 0 || ctx->n_cp == 0 || N < 3 || (S.n_groups > 2 && std::getenv("OMO_SORTED_CURVES") == nullptr)) return OMO_OK;
+    if (ctx->perm_mode != 1 || nk == 0 || ctx->n_cp == 0 || N < 3) return OMO_OK;
     // predicted iteration count of every (keyed channel, sample)
     std::vector<unsigned char> cnt((size_t)nk * N, 0);
     const std::vector<double>& x = ctx->x0;
