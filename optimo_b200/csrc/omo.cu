@@ -1053,9 +1053,11 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
     // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
     // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
     const size_t bytes = (size_t)B * W * sizeof(double);
-    // a chunk is at least 4 MB and at least ~8 waves of objective blocks
-    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 4736;
-    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)4 << 20), by_work)));   // 4 measured best on stick240 (1.26 ms; 2: 1.30, 8: 1.33)
+    // a chunk is at least 1 MB and at least ~3 waves of objective blocks (chunks alternate between two compute streams, so a chunk's
+    // partial last wave is not lost); at most 4: measured best on stick240 (4: 1.097 ms, 6: 1.108, 8: 1.121). The slices a rank of an
+    // 8-GPU job gets (3.2 MB) still travel in two chunks, so that their copy overlaps their evaluation.
+    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 2368;
+    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)1 << 20), by_work)));
     if (const char* e = std::getenv("OMO_EVAL_CHUNKS")) n_chunks = std::max(1, std::min(8, std::min(B, std::atoi(e))));
     auto evaluate = [&](int b0, int nb) -> omo_status {
         if (expand) {
