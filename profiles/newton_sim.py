@@ -120,3 +120,33 @@ c=Core(scene); x0=c.GetDescriptor()
 proxyA=sim_x(scene,x0)
 print('tree G=12 proxy=x0', cost_sorted(its,proxyA,12))
 print('tree G=12 proxy=cand0', cost_sorted(its[1:],its[0],12))
+
+print("---- sample permutation (all channels of a group keep their lane; lanes take samples sorted by predicted cost) ----")
+def cost_sample_perm(its, proxy, G):
+    B,C,N=its.shape
+    tot_lock=tot_perm=0
+    for b in range(B):
+        for tile0 in range(0,N,124):
+            s0=max(tile0-2,0); s1=min(s0+128,N)
+            if s1-s0<128: continue
+            for g0 in range(0,C,G):
+                k=its[b,g0:g0+G,s0:s1]
+                g=k.shape[0]; ntri=(g+2)//3
+                for w in range(4):
+                    for t in range(ntri):
+                        tot_lock+=k[3*t:3*t+3,32*w:32*w+32].max()*3
+                pr=proxy[g0:g0+G,s0:s1].sum(axis=0)           # predicted cost of a sample = sum over the group's channels
+                order=np.argsort(-pr,kind='stable')
+                kp=k[:,order]
+                for w in range(4):
+                    for t in range(ntri):
+                        tot_perm+=kp[3*t:3*t+3,32*w:32*w+32].max()*3
+    return tot_lock,tot_perm
+scene=synthetic.tree_scene(64,200)
+its=sim(scene,3)
+c=Core(scene); x0=c.GetDescriptor()
+proxyA=sim_x(scene,x0)
+print('tree G=12 sample-perm proxy=x0', cost_sample_perm(its,proxyA,12))
+scene=synthetic.stick_240(json.load(open(ROOT + '/tests/golden/scenes/stick-figure.json')))
+its=sim(scene,8); c=Core(scene); x0=c.GetDescriptor(); proxyA=sim_x(scene,x0)
+print('stick240 G=6 sample-perm proxy=x0', cost_sample_perm(its,proxyA,6))
