@@ -146,6 +146,24 @@ omo_status omo_eval_device(omo_ctx* ctx, const double* dX, int B, double* d_f_ou
  * gathers its shard with NCCL. Asynchronous on the ctx stream unless `sync` != 0. */
 omo_status omo_eval_host_in(omo_ctx* ctx, const double* X, int B, double* d_f_out, double* d_terms_out, int sync);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it). omo_eval_device with the scratch of the
+ * prepare -> objective -> finish chain (prepared control points, segment records, per-tile segment indices, tile partial sums) in a
+ * file-scope `static __device__` array of OMO_STATIC_SCRATCH_BYTES instead of the context's work buffers: the call makes no
+ * cudaMalloc / cudaFree / module load and creates no events; dX, d_f_out[B] and the optional d_terms_out[3B] are the caller's
+ * device memory. It always runs the table-driven kernel (loading a scene-specialised module allocates), so it agrees with
+ * omo_eval_device bit for bit where that one takes the table-driven kernel too (launches below 64 K sample-evals) and to ~1e-13
+ * relative otherwise.
+ *   - OMO_BAD_ARG when B candidates of this scene and window need more scratch than the array holds (the message names the largest
+ *     B that fits: ~21 KB per candidate for the 160 control points x 10 tiles of BASELINE configs[3], i.e. ~390 candidates).
+ *   - OMO_NOT_READY until the state derived from window / weights / x_original has been built by an allocating entry point
+ *     (omo_get_p_original or any omo_eval*, once after the omo_set_* calls).
+ *   - every device that loads libomo.so holds the array until the process exits, and every call on a device shares it: two calls that
+ *     overlap on the GPU (two contexts, or two streams) race. Nothing in it has to start at zero; it keeps the last call's contents.
+ * Asynchronous on the ctx stream unless `sync` != 0. */
+#define OMO_STATIC_SCRATCH_BYTES (8u << 20)
+omo_status omo_eval_device_static(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync);
+
 /* One evaluation that also fills the OptimizationCache of the reference (core.h:120-152): each of
  * q, qd, qdd, tau is [N_s * dof] sample-major, local_cost is [N_s]; any of them may be NULL. */
 omo_status omo_eval_cached(omo_ctx* ctx, const double* x, double* f_out, omo_terms* terms_out, double* q, double* qd,

@@ -137,6 +137,7 @@ _OMO_SIG = {
     "omo_eval": (ci, [_vp, _dp, ci, _dp, _dp]),
     "omo_eval_free": (ci, [_vp, _dp, _ip, ci, _dp, ci, _dp, _dp]),
     "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
+    "omo_eval_device_static": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_set_batch_hint": (ci, [_vp, ci]),
     "omo_eval_host_in": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
@@ -276,6 +277,10 @@ class Engine:
 
     def eval_device(self, dX, B, dF, dTerms=None, sync=True):
         self._ck(_omo.omo_eval_device(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device")
+
+    def eval_device_static(self, dX, B, dF, dTerms=None, sync=True):
+        """omo_eval_device_static: the same batch with its scratch in the library's static device array (no allocation)."""
+        self._ck(_omo.omo_eval_device_static(self.h, dX, B, dF, dTerms, int(sync)), "omo_eval_device_static")
 
     def set_batch_hint(self, total):
         """This engine evaluates slices of a batch of `total` candidates (kernel choice by the whole batch; 0 = off)."""

@@ -2021,3 +2021,116 @@ omo_status omo_selftest_division(omo_ctx* ctx, const double* num, const double* 
 }
 
 }  // extern "C"
+
+// ---- the batch objective without a single allocation (include/omo.h: omo_eval_device_static) -------------------------------------
+// Scratch of the prepare -> objective -> finish chain in a file-scope array instead of the context's cudaMalloc'ed work buffers.
+// Every device that loads libomo.so holds OMO_STATIC_SCRATCH_BYTES of it until the process exits; every call on a device shares it.
+static __device__ __align__(256) unsigned char g_static_scratch[OMO_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_static_scratch` is only the host-side stand-in of the symbol: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+std::mutex g_static_scratch_mutex;
+unsigned char* g_static_scratch_addr[64] = {};
+
+omo_status static_scratch_address(omo_ctx* ctx, unsigned char** out)
+{
+    std::lock_guard<std::mutex> g(g_static_scratch_mutex);
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return fail(ctx, OMO_BAD_ARG, "device index out of range");
+    if (!g_static_scratch_addr[dev]) {
+        OMO_CUDA(cudaSetDevice(dev));
+        void* p = nullptr;
+        OMO_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u) != 0) return fail(ctx, OMO_CUDA_ERROR, "cudaGetSymbolAddress(g_static_scratch) returned an unusable address");
+        g_static_scratch_addr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_scratch_addr[dev];
+    return OMO_OK;
+}
+
+// The work buffers of ensure_capacity for B candidates, carved out of one block (each 256-byte aligned).
+struct StaticLayout {
+    size_t prep = 0, dparam = 0, seg = 0, partial = 0, flags = 0, tile_seg = 0, total = 0;
+    StaticLayout(const omo_ctx* ctx, size_t B)
+    {
+        const size_t tiles = (size_t)std::max(ctx->n_tiles, 1), n_cp = (size_t)ctx->n_cp;
+        size_t off = 0;
+        auto take = [&off](size_t bytes) { const size_t at = off; off = (off + std::max<size_t>(bytes, 1) + 255) & ~(size_t)255; return at; };
+        prep = take(B * 6 * n_cp * sizeof(double));
+        dparam = take(B * (size_t)prep_parts(ctx) * sizeof(double));
+        seg = take((B * n_cp + OMO_SEGW) * OMO_SEGD * sizeof(double));
+        partial = take(B * tiles * 2 * sizeof(double));
+        flags = take(B * sizeof(unsigned));
+        tile_seg = take(B * tiles * (size_t)std::max(ctx->hs.n_keyed, 1) * sizeof(unsigned short));
+        total = off;
+    }
+};
+
+// Points the context's work-buffer fields at the static block for the duration of one call and takes the choices that would
+// allocate (specialised-kernel module load, sorted work lists, timing events) off the table; everything is put back on exit.
+struct StaticScratchScope {
+    omo_ctx* c;
+    double *prep, *dparam, *partial, *seg; unsigned* flags; unsigned short* tile_seg;
+    int row0, jit_mode, batch_hint; bool prefer_jit, timing;
+    StaticScratchScope(omo_ctx* ctx, unsigned char* base, const StaticLayout& L)
+        : c(ctx), prep(ctx->d_prep), dparam(ctx->d_dparam), partial(ctx->d_partial), seg(ctx->d_seg), flags(ctx->d_flags), tile_seg(ctx->d_tile_seg),
+          row0(ctx->row0), jit_mode(ctx->jit_mode), batch_hint(ctx->batch_hint), prefer_jit(ctx->prefer_jit), timing(ctx->timing)
+    {
+        c->d_prep = reinterpret_cast<double*>(base + L.prep); c->d_dparam = reinterpret_cast<double*>(base + L.dparam);
+        c->d_seg = reinterpret_cast<double*>(base + L.seg); c->d_partial = reinterpret_cast<double*>(base + L.partial);
+        c->d_flags = reinterpret_cast<unsigned*>(base + L.flags); c->d_tile_seg = reinterpret_cast<unsigned short*>(base + L.tile_seg);
+        c->row0 = 0; c->jit_mode = 0; c->batch_hint = 0; c->prefer_jit = false; c->timing = false;
+    }
+    ~StaticScratchScope()
+    {
+        c->d_prep = prep; c->d_dparam = dparam; c->d_partial = partial; c->d_seg = seg; c->d_flags = flags; c->d_tile_seg = tile_seg;
+        c->row0 = row0; c->jit_mode = jit_mode; c->batch_hint = batch_hint; c->prefer_jit = prefer_jit; c->timing = timing;
+    }
+};
+
+}  // namespace
+
+extern "C" omo_status omo_eval_device_static(omo_ctx* ctx, const double* dX, int B, double* d_f_out, double* d_terms_out, int sync)
+{
+    DeviceLock device_lock(ctx);
+    if (!ctx || !dX || !d_f_out || B < 0) return fail(ctx, OMO_BAD_ARG, "bad argument");
+    if (B == 0) return OMO_OK;
+    if (!ctx->have_window || !ctx->have_weights || !ctx->have_original) return fail(ctx, OMO_NOT_READY, "window / weights / x_original not set");
+    // the state derived from them (cost weights, p_original, the pruned bodies' share of the cost) lives in buffers that the allocating
+    // entry points build: this one refuses to
+    if (ctx->wcost_dirty || ctx->p_orig_dirty)
+        return fail(ctx, OMO_NOT_READY, "omo_eval_device_static allocates nothing: after omo_set_window / omo_set_weights / omo_set_original call "
+                                         "omo_get_p_original (or any omo_eval*) once, outside the no-allocation region, to build the derived state");
+    const StaticLayout L(ctx, (size_t)B);
+    if (L.total > (size_t)OMO_STATIC_SCRATCH_BYTES) {
+        int fit = 0, over = B;   // largest batch of this scene and window that fits (the layout grows with B)
+        while (over - fit > 1) {
+            const int mid = fit + (over - fit) / 2;
+            if (StaticLayout(ctx, (size_t)mid).total <= (size_t)OMO_STATIC_SCRATCH_BYTES) fit = mid; else over = mid;
+        }
+        return fail(ctx, OMO_BAD_ARG, "omo_eval_device_static: " + std::to_string(B) + " candidates need " + std::to_string(L.total) + " bytes of scratch, the static array holds " +
+                                          std::to_string((size_t)OMO_STATIC_SCRATCH_BYTES) + " (at most " + std::to_string(fit) + " candidates of this scene and window per call)");
+    }
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    omo_status st = static_scratch_address(ctx, &base);
+    if (st != OMO_OK) return st;
+    if ((st = activate_scene(ctx)) != OMO_OK) return st;   // a copy into constant memory when another context used the device in between; no allocation
+    {
+        // Nothing in the scratch has to start at zero: prepare_kernel writes every prep / seg / tile_seg / dparam / flag entry of the B rows
+        // (flag words shared by several blocks are preset by run_prepare's memset) and the objective kernel every partial sum before
+        // finish_kernel reads them, so the previous call's contents are never observed.
+        StaticScratchScope scope(ctx, base, L);
+        if ((st = run_prepare(ctx, dX, B)) != OMO_OK) return st;
+        OmoEvalParams P;
+        fill_params(ctx, P);
+        P.perm = nullptr;   // the sorted work lists belong to the specialised kernel's launches
+        const bool fk = (ctx->w_traj != 0.0) || ctx->n_ik > 0;
+        P.p_orig = (ctx->w_traj != 0.0) ? ctx->d_p_orig : nullptr;
+        if ((st = launch_objective(ctx, P, B, fk, false, d_f_out, d_terms_out)) != OMO_OK) return st;
+    }
+    if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+    return OMO_OK;
+}
