@@ -659,9 +659,45 @@ def run_multi_gpu(G, args):
     sampler = ClockSampler(G.local) if rank == 0 else None
     if sampler:
         sampler.start()
-    ms_dev, wall_dev, (k_ms, k_n), launches = G.timed(eng, strong_device, args.steps, args.warmup, kernel_timing=True)
+    ms_nccl, wall_dev, (k_ms, k_n), launches = G.timed(eng, strong_device, args.steps, args.warmup, kernel_timing=True)
     ms_e2e, wall_e2e, _, _ = G.timed(eng, strong_e2e, args.steps, max(args.warmup, 3))
     f_strong = np.concatenate([dAll.cpu().numpy()[r * pad: r * pad + shard_range(B, r, world)[1]] for r in range(world)])
+
+    # ---- the same step with the gather fused into the kernel that forms f (omo_peer_gather_*: NVLink / NVSwitch peer stores + flags, no
+    # NCCL call). Used for the headline when every rank could map its peers and the gathered values equal the NCCL path's bit for bit.
+    peer = {"available": False}
+    pg = None
+    try:
+        from optimo_b200.core import PeerGather
+
+        def exchange(handle):
+            got = [None] * world
+            dist.all_gather_object(got, handle)
+            return got
+        pg = PeerGather(eng, rank, world, B, exchange)
+        ok = 1
+    except Exception as e:   # noqa: BLE001
+        peer["error"] = str(e)[:300]
+        ok = 0
+    t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
+    dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+    ms_dev, gather_used = ms_nccl, "nccl all_gather of f inside the timed step"
+    if int(t_ok.item()) == 1:
+        def strong_device_peer():
+            pg.eval(dXs.data_ptr(), nb, b0, sync=False)
+        ms_peer, wall_peer, (k_ms_p, k_n_p), launches_p = G.timed(eng, strong_device_peer, args.steps, args.warmup, kernel_timing=True)
+        f_peer = eng.d2h(pg.values(), (B,))
+        same = bool(np.array_equal(f_peer, f_strong)) and pg.error() == 0
+        t_same = torch.tensor([1 if same else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t_same, op=dist.ReduceOp.MIN)
+        same = int(t_same.item()) == 1
+        peer = {"available": True, "ms_per_step": ms_peer, "nccl_ms_per_step": ms_nccl, "bit_identical_to_nccl_path_on_every_rank": same,
+                "api": "omo_peer_gather_eval: finish_kernel's sums stored into every rank's gathered array through cudaIpc-mapped peer memory, flags, wait -- one launch"}
+        if same and ms_peer < ms_nccl:
+            ms_dev, wall_dev, k_ms, k_n, launches = ms_peer, wall_peer, k_ms_p, k_n_p, launches_p
+            gather_used = "NVLink / NVSwitch peer stores from the kernel that forms f (omo_peer_gather_eval); nccl all_gather measured beside it (peer_gather.nccl_ms_per_step)"
+    elif "error" not in peer:
+        peer["error"] = "another rank could not map its peers"
 
     # ---- weak scaling: every rank its own 4096 candidates (the r01 figure) ------------------------------------------
     Ww = W
@@ -795,7 +831,7 @@ def run_multi_gpu(G, args):
             "metric": METRIC, "value": n_total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": W.desc, "candidates_total": B, "candidates_per_gpu": nb, "samples_per_candidate": W.N_s, "joints": W.J, "descriptor": W.D,
-                       "split": "omo_shard_range over candidates; every rank evaluates its slice", "gather": "nccl all_gather of f inside the timed step",
+                       "split": "omo_shard_range over candidates; every rank evaluates its slice", "gather": gather_used,
                        "l2": "flushed between timed iterations (256 MiB memset)"},
             "clocks": sampler.summary() if sampler else None,
             "e2e": {"value": n_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
@@ -808,11 +844,15 @@ def run_multi_gpu(G, args):
                              "api": "omo_eval_grad_columns(col_begin, col_count) per rank + nccl all_gather + omo_grad_from_columns on rank 0's host",
                              "bit_identical_to_one_gpu": grad_same},
             "gather_latency": gather,
+            "peer_gather": peer,
             "single_process": single,
             "objective_evals_per_s": B / (ms_dev * 1e-3), "frame_evals_per_s": n_total / (ms_dev * 1e-3) / 5.0,
             "wall_s": {"device_loop": wall_dev, "e2e_loop": wall_e2e},
         }
         print(json.dumps(line), flush=True)
+    if pg is not None:
+        dist.barrier()      # nobody unmaps a peer that may still be written to
+        pg.close()
     dist.destroy_process_group()
 
 

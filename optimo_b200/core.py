@@ -139,6 +139,12 @@ _OMO_SIG = {
     "omo_eval_device": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_device_static": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_set_batch_hint": (ci, [_vp, ci]),
+    "omo_peer_gather_create": (ci, [_vp, ci, ci, ci, C.POINTER(_vp), C.c_char_p]),
+    "omo_peer_gather_connect": (ci, [_vp, C.c_char_p]),
+    "omo_peer_gather_eval": (ci, [_vp, _vp, ci, ci, ci]),
+    "omo_peer_gather_values": (_vp, [_vp]),
+    "omo_peer_gather_error": (ci, [_vp]),
+    "omo_peer_gather_destroy": (None, [_vp]),
     "omo_eval_host_in": (ci, [_vp, _vp, ci, _vp, _vp, ci]),
     "omo_eval_grad": (ci, [_vp, _dp, _ip, ci, cd, _dp, _dp, _dp]),
     "omo_eval_grad_columns": (ci, [_vp, _dp, _ip, ci, cd, ci, ci, _vp, ci]),
@@ -391,6 +397,40 @@ class Engine:
         v = C.c_double(0.0)
         self._ck(_omo.omo_measure_dfma_peak(self.h, C.byref(v)), "omo_measure_dfma_peak")
         return v.value
+
+
+class PeerGather:
+    """omo_peer_gather (include/omo.h): the f values of ONE batch evaluated by several PROCESSES, one GPU each, gathered into every
+    rank's device memory by the kernel that forms them (NVLink / NVSwitch peer stores, no NCCL call). `exchange(handle) -> [handles in
+    rank order]` is the caller's transport (torch.distributed.all_gather_object, MPI, files)."""
+    HANDLE_BYTES = 64
+
+    def __init__(self, engine, rank, world, capacity, exchange):
+        self.eng, self.rank, self.world, self.capacity = engine, rank, world, capacity
+        h = _vp()
+        buf = C.create_string_buffer(self.HANDLE_BYTES)
+        engine._ck(_omo.omo_peer_gather_create(engine.h, rank, world, capacity, C.byref(h), buf), "omo_peer_gather_create")
+        self.h = h.value
+        handles = exchange(buf.raw)
+        if len(handles) != world or any(len(x) != self.HANDLE_BYTES for x in handles):
+            raise EngineError("peer gather: need one 64-byte handle per rank")
+        engine._ck(_omo.omo_peer_gather_connect(self.h, b"".join(handles)), "omo_peer_gather_connect")
+
+    def eval(self, dX, B_local, first, sync=True):
+        """Evaluates this rank's slice [first, first + B_local) of the batch; afterwards values() holds every rank's f."""
+        self.eng._ck(_omo.omo_peer_gather_eval(self.h, dX, B_local, first, int(sync)), "omo_peer_gather_eval")
+
+    def values(self):
+        """Device address of the gathered f (capacity doubles) of the last call."""
+        return _omo.omo_peer_gather_values(self.h)
+
+    def error(self):
+        return _omo.omo_peer_gather_error(self.h)
+
+    def close(self):
+        if self.h:
+            _omo.omo_peer_gather_destroy(self.h)
+            self.h = None
 
 
 class MultiEngine:

@@ -144,6 +144,9 @@ struct omo_ctx {
     double* h_self_out = nullptr;               // mapped pinned host memory the kernel writes f into: [max(4, self_out_cap)]
     double* d_self_out = nullptr;               // its device alias
     int self_out_cap = 0;
+    double self_seq = 0.0;                      // completion word of the last self-preparing launch that wrote to h_self_out (slot [self_out_cap])
+    bool self_spin_pending = false;             // ... and whether the host may wait on it instead of on the stream
+    int self_spin_mode = -1;                    // OMO_SPIN=0: always wait on the stream
     unsigned long long self_launches = 0;
 
     // sorted curve work lists (OmoEvalParams::perm), rebuilt with x_original / the window
@@ -154,6 +157,9 @@ struct omo_ctx {
     double *d_adj_L = nullptr, *d_adj_G = nullptr, *d_adj_contrib = nullptr, *d_adj_gfull = nullptr, *d_adj_gout = nullptr, *d_oroot = nullptr;
     size_t adj_cap = 0; int adj_F_cap = 0; int adj_max_sub = 0;
     unsigned long long adj_calls = 0;
+
+    // omo_peer_gather_eval in flight: the finish step of the batch launches is the fused finish + peer exchange kernel
+    struct omo_peer_gather* peer = nullptr;
 
     // counters / timing
     unsigned long long* d_counters = nullptr;
@@ -619,6 +625,47 @@ omo_status launch_jit(omo_ctx* ctx, omo_ctx::JitKernel* k, const OmoEvalParams& 
 
 omo_status build_perm(omo_ctx* ctx);
 
+}  // namespace
+
+// Gather of a multi-process job over NVLink / NVSwitch peer memory (include/omo.h: omo_peer_gather_*).
+struct omo_peer_gather {
+    omo_ctx* ctx = nullptr;
+    int rank = 0, world = 1, capacity = 0;
+    unsigned char* d_block = nullptr;          // this rank's allocation: [2][capacity] doubles, then [world] flag words
+    void* opened[OMO_MAX_PEERS] = {};          // cudaIpcOpenMemHandle mappings of the other ranks' allocations
+    double* buf[OMO_MAX_PEERS] = {};
+    unsigned long long* flag[OMO_MAX_PEERS] = {};
+    unsigned* d_ticket = nullptr;
+    int* h_error = nullptr; int* d_error = nullptr;   // mapped host word: a wait that timed out
+    unsigned long long seq = 0;
+    bool connected = false;
+    long long first = 0;                       // arguments of the call in flight
+};
+
+namespace {
+
+size_t peer_flag_offset(const int capacity) { return (((size_t)2 * capacity * sizeof(double)) + 255) & ~(size_t)255; }
+
+// The finish step of a batch launch: finish_kernel, or -- inside omo_peer_gather_eval -- its fusion with the peer exchange.
+omo_status launch_finish(omo_ctx* ctx, int B, int n_tiles, double* d_f, double* d_terms)
+{
+    if (omo_peer_gather* g = ctx->peer) {
+        omo::OmoPeerParams G;
+        std::memset(&G, 0, sizeof(G));
+        for (int p = 0; p < g->world; ++p) { G.buf[p] = g->buf[p]; G.flag[p] = g->flag[p]; }
+        G.world = g->world; G.rank = g->rank;
+        G.offset = (long long)(g->seq & 1ull) * g->capacity + g->first;
+        G.seq = g->seq; G.ticket = g->d_ticket; G.error = g->d_error;
+        G.timeout_cycles = 4000000000ll;   // ~2 s at 1.9 GHz
+        omo::finish_exchange_kernel<<<std::max((B + 127) / 128, 1), 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, n_tiles, prep_parts(ctx), G);
+    } else {
+        omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, n_tiles, prep_parts(ctx), d_f, d_terms);
+    }
+    OMO_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return OMO_OK;
+}
+
 // Launches the objective kernel over B candidates and the finish kernel that adds the tile partials.
 // d_item_map (optional): the launch covers only the n_items listed (candidate, tile) pairs and leaves the sums to the caller.
 omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool out, double* d_f, double* d_terms,
@@ -647,10 +694,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
         if (omo_ctx::JitKernel* k = acquire_jit(ctx, fk, ik, count)) {
             if ((st = launch_jit(ctx, k, P, B, plan.n_tiles)) != OMO_OK) return st;
             if (d_item_map) return OMO_OK;
-            omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
-            OMO_CUDA(cudaGetLastError());
-            ctx->launches += 1;
-            return OMO_OK;
+            return launch_finish(ctx, B, plan.n_tiles, d_f, d_terms);
         }
         if (mode == 1) return fail(ctx, OMO_CUDA_ERROR, "OMO_JIT=1 but the specialised kernel is unavailable: " + ctx->jit_log);
     }
@@ -665,10 +709,7 @@ omo_status launch_objective(omo_ctx* ctx, OmoEvalParams& P, int B, bool fk, bool
     else st = count ? launch_objective_t<false, false, false, true>(ctx, P, B, plan) : launch_objective_t<false, false, false, false>(ctx, P, B, plan);
     if (st != OMO_OK) return st;
     if (d_item_map) return OMO_OK;
-    omo::finish_kernel<<<(B + 127) / 128, 128, 0, ctx->stream>>>(sc_partial(ctx), sc_dparam(ctx), B, plan.n_tiles, prep_parts(ctx), d_f, d_terms);
-    OMO_CUDA(cudaGetLastError());
-    ctx->launches += 1;
-    return OMO_OK;
+    return launch_finish(ctx, B, plan.n_tiles, d_f, d_terms);
 }
 
 void fill_params(const omo_ctx* ctx, OmoEvalParams& P)
@@ -980,10 +1021,39 @@ omo_status ensure_self_buffers(omo_ctx* ctx, int rows)
         const int cap = std::max(rows, 256);
         OMO_CUDA(cudaStreamSynchronize(ctx->stream));
         if (ctx->h_self_out) { cudaFreeHost(ctx->h_self_out); ctx->h_self_out = nullptr; }
-        OMO_CUDA(cudaHostAlloc((void**)&ctx->h_self_out, (size_t)cap * sizeof(double), cudaHostAllocMapped));
+        OMO_CUDA(cudaHostAlloc((void**)&ctx->h_self_out, (size_t)(cap + 1) * sizeof(double), cudaHostAllocMapped));   // + the completion word
         OMO_CUDA(cudaHostGetDevicePointer((void**)&ctx->d_self_out, ctx->h_self_out, 0));
+        ctx->h_self_out[cap] = 0.0;
         ctx->self_out_cap = cap;
     }
+    return OMO_OK;
+}
+
+// Waits for the self-preparing launch that was queued last. Where it writes into the mapped host buffer the kernel's last block
+// sets a completion word behind the outputs (system-scope fence first), and the host reads that word in a loop: the values are
+// there a PCIe write after the kernel produced them, without the driver's completion path. The stream is asked now and then
+// (a faulted kernel never sets the word), and is what is waited on when polling is off (OMO_SPIN=0) or the output lives elsewhere.
+omo_status wait_self(omo_ctx* ctx)
+{
+    if (ctx->self_spin_pending) {
+        ctx->self_spin_pending = false;
+        const volatile double* flag = ctx->h_self_out + ctx->self_out_cap;
+        for (unsigned spin = 1;; ++spin) {
+            if (*flag == ctx->self_seq) return OMO_OK;
+            if ((spin & 2047u) == 0u) {
+                const cudaError_t q = cudaStreamQuery(ctx->stream);
+                if (q == cudaSuccess) {
+                    if (*flag == ctx->self_seq) return OMO_OK;
+                    return fail(ctx, OMO_CUDA_ERROR, "self-preparing kernel finished without setting its completion word");
+                }
+                if (q != cudaErrorNotReady) { ctx->err = std::string("self-preparing launch: ") + cudaGetErrorString(q); return OMO_CUDA_ERROR; }
+            }
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+        }
+    }
+    OMO_CUDA(cudaStreamSynchronize(ctx->stream));
     return OMO_OK;
 }
 
@@ -1013,6 +1083,16 @@ omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_ro
     P.self_x0 = ctx->d_x0; P.self_wparam = ctx->d_wparam;
     P.self_dparam = ctx->d_self_dparam; P.self_out = out; P.self_counter = ctx->d_self_counter;
     P.self_h = h; P.self_col_begin = col_begin; P.self_rows = rows; P.self_base_row = base_row; P.self_cyclic = ctx->cyclic; P.self_D = ctx->D;
+    // results into the context's mapped host buffer: the last block also sets a completion word there, which the host polls
+    // (wait_self) instead of paying the stream synchronisation's round trip through the driver
+    if (ctx->self_spin_mode < 0) { const char* e = std::getenv("OMO_SPIN"); ctx->self_spin_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
+    ctx->self_spin_pending = false;
+    P.self_done = nullptr; P.self_seq = 0.0;
+    if (out == ctx->d_self_out && ctx->self_spin_mode == 1 && !ctx->timing) {
+        ctx->self_seq += 1.0;
+        P.self_done = ctx->d_self_out + ctx->self_out_cap; P.self_seq = ctx->self_seq;
+        ctx->self_spin_pending = true;
+    }
     omo_jit::Api& a = omo_jit::api();
     if (k->uploaded_version != ctx->scene_version) {
         OMO_CUDA(cudaMemcpyAsync(reinterpret_cast<void*>(k->d_scene), &ctx->hs, sizeof(OmoDevScene), cudaMemcpyHostToDevice, ctx->stream));
@@ -1352,7 +1432,7 @@ omo_status omo_eval(omo_ctx* ctx, const double* X, int B, double* f_out, omo_ter
         bool launched = false;
         if ((st = launch_self(ctx, X, 1, -1, nullptr, 0, nullptr, nullptr, nullptr, 0.0, 0, ctx->d_self_out, &launched)) != OMO_OK) return st;
         if (launched) {
-            OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+            if ((st = wait_self(ctx)) != OMO_OK) return st;
             *f_out = ctx->h_self_out[0];
             if (terms_out) { terms_out->C = ctx->h_self_out[1]; terms_out->D_param = ctx->h_self_out[2]; terms_out->D_traj = ctx->h_self_out[3]; }
             return OMO_OK;
@@ -1622,7 +1702,8 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
         if ((st = launch_self(ctx, x, rows, col_count, ctx->d_items, (int)ctx->h_items.size(), ctx->d_lohi, ctx->d_lohi + col_count, ctx->d_free, h, col_begin,
                               d_f_cols, &launched)) != OMO_OK) return st;
         if (launched) {
-            if (sync) OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (sync) return wait_self(ctx);
+            ctx->self_spin_pending = false;   // the caller synchronises the stream itself
             return OMO_OK;
         }
     }
@@ -1672,7 +1753,7 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     if (P + 1 <= kSelfMaxRows && self_usable(ctx)) {
         // the column values are written straight into mapped host memory (by the self-preparing kernel, or by finish_sparse_kernel
         // if that launch is not to be had): no copy-out
-        if ((st = ensure_self_buffers(ctx, P)) != OMO_OK) return st;
+        if ((st = ensure_self_buffers(ctx, P + 1)) != OMO_OK) return st;   // + the base row: launch_self must not move the buffer `out` points into
         if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_self_out, 1)) != OMO_OK) return st;
         std::copy(ctx->h_self_out, ctx->h_self_out + P, ctx->h_cols.begin());
     } else {
@@ -2025,6 +2106,125 @@ omo_status omo_selftest_division(omo_ctx* ctx, const double* num, const double* 
 }
 
 }  // extern "C"
+
+// ---- multi-process gather over NVLink / NVSwitch peer memory (include/omo.h: omo_peer_gather_*) -----------------------------------
+extern "C" omo_status omo_peer_gather_create(omo_ctx* ctx, int rank, int world, int capacity, omo_peer_gather** out, unsigned char* handle_out)
+{
+    DeviceLock device_lock(ctx);
+    if (!ctx || !out || !handle_out || world < 1 || world > OMO_MAX_PEERS || rank < 0 || rank >= world || capacity < 1)
+        return fail(ctx, OMO_BAD_ARG, "omo_peer_gather_create: bad argument (1 <= world <= 16, 0 <= rank < world, capacity >= 1)");
+    static_assert(sizeof(cudaIpcMemHandle_t) <= OMO_IPC_HANDLE_BYTES, "OMO_IPC_HANDLE_BYTES is too small for cudaIpcMemHandle_t");
+    *out = nullptr;
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    omo_peer_gather* g = new omo_peer_gather();
+    g->ctx = ctx; g->rank = rank; g->world = world; g->capacity = capacity;
+    const size_t bytes = peer_flag_offset(capacity) + (size_t)OMO_MAX_PEERS * sizeof(unsigned long long);
+    cudaError_t e = cudaMalloc((void**)&g->d_block, bytes);
+    if (e == cudaSuccess) e = cudaMemset(g->d_block, 0, bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&g->d_ticket, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(g->d_ticket, 0, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&g->h_error, sizeof(int), cudaHostAllocMapped);
+    if (e == cudaSuccess) { *g->h_error = 0; e = cudaHostGetDevicePointer((void**)&g->d_error, g->h_error, 0); }
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, g->d_block);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();   // the zeroed flags are in place before any peer can learn the handle
+    if (e != cudaSuccess) {
+        ctx->err = std::string("omo_peer_gather_create: ") + cudaGetErrorString(e);
+        omo_peer_gather_destroy(g);
+        return e == cudaErrorMemoryAllocation ? OMO_OOM : OMO_CUDA_ERROR;
+    }
+    std::memset(handle_out, 0, OMO_IPC_HANDLE_BYTES);
+    std::memcpy(handle_out, &h, sizeof(h));
+    g->buf[rank] = reinterpret_cast<double*>(g->d_block);
+    g->flag[rank] = reinterpret_cast<unsigned long long*>(g->d_block + peer_flag_offset(capacity));
+    *out = g;
+    return OMO_OK;
+}
+
+extern "C" omo_status omo_peer_gather_connect(omo_peer_gather* g, const unsigned char* handles)
+{
+    if (!g || !handles) return OMO_BAD_ARG;
+    omo_ctx* ctx = g->ctx;
+    DeviceLock device_lock(ctx);
+    OMO_CUDA(cudaSetDevice(ctx->device));
+    for (int p = 0; p < g->world; ++p) {
+        if (p == g->rank || g->opened[p]) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)p * OMO_IPC_HANDLE_BYTES, sizeof(h));
+        void* ptr = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            ctx->err = "omo_peer_gather_connect: cudaIpcOpenMemHandle(rank " + std::to_string(p) + "): " + cudaGetErrorString(e) +
+                       " (no peer access between the devices, or the ranks do not share an IPC namespace): gather with NCCL instead";
+            return OMO_NCCL_ERROR;
+        }
+        g->opened[p] = ptr;
+        g->buf[p] = reinterpret_cast<double*>(ptr);
+        g->flag[p] = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(ptr) + peer_flag_offset(g->capacity));
+    }
+    g->connected = true;
+    return OMO_OK;
+}
+
+extern "C" omo_status omo_peer_gather_eval(omo_peer_gather* g, const double* dX, int B_local, int first, int sync)
+{
+    if (!g) return OMO_BAD_ARG;
+    omo_ctx* ctx = g->ctx;
+    DeviceLock device_lock(ctx);
+    if (!g->connected) return fail(ctx, OMO_NOT_READY, "omo_peer_gather_connect has not been called");
+    if ((!dX && B_local > 0) || B_local < 0 || first < 0 || (long long)first + B_local > g->capacity)
+        return fail(ctx, OMO_BAD_ARG, "omo_peer_gather_eval: the slice [first, first + B_local) does not fit the gathered array");
+    omo_status st = ensure_ready(ctx);
+    if (st != OMO_OK) return st;
+    g->seq += 1;
+    g->first = first;
+    if (B_local > 0) {
+        ctx->peer = g;
+        st = eval_device_impl(ctx, dX, B_local, ctx->d_f, nullptr);
+        ctx->peer = nullptr;
+        if (st != OMO_OK) return st;
+    } else {
+        // a rank without candidates still takes part in the exchange: flags only
+        if ((st = ensure_capacity(ctx, 1)) != OMO_OK) return st;
+        ctx->peer = g;
+        st = launch_finish(ctx, 0, std::max(ctx->n_tiles, 1), nullptr, nullptr);
+        ctx->peer = nullptr;
+        if (st != OMO_OK) return st;
+    }
+    if (sync) {
+        OMO_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (*static_cast<volatile int*>(g->h_error) != 0) {
+            *g->h_error = 0;
+            return fail(ctx, OMO_NCCL_ERROR, "omo_peer_gather_eval: a rank's slice did not arrive within the time-out");
+        }
+    }
+    return OMO_OK;
+}
+
+extern "C" const double* omo_peer_gather_values(const omo_peer_gather* g)
+{
+    return g ? g->buf[g->rank] + (size_t)(g->seq & 1ull) * g->capacity : nullptr;
+}
+
+extern "C" int omo_peer_gather_error(omo_peer_gather* g)
+{
+    if (!g || !g->h_error) return 0;
+    const int e = *static_cast<volatile int*>(g->h_error);
+    *g->h_error = 0;
+    return e;
+}
+
+extern "C" void omo_peer_gather_destroy(omo_peer_gather* g)
+{
+    if (!g) return;
+    if (g->ctx) { cudaSetDevice(g->ctx->device); if (g->ctx->stream) cudaStreamSynchronize(g->ctx->stream); }
+    for (int p = 0; p < OMO_MAX_PEERS; ++p) if (g->opened[p]) cudaIpcCloseMemHandle(g->opened[p]);
+    if (g->d_block) cudaFree(g->d_block);
+    if (g->d_ticket) cudaFree(g->d_ticket);
+    if (g->h_error) cudaFreeHost(g->h_error);
+    delete g;
+}
 
 // ---- the batch objective without a single allocation (include/omo.h: omo_eval_device_static) -------------------------------------
 // Scratch of the prepare -> objective -> finish chain in a file-scope array instead of the context's cudaMalloc'ed work buffers.

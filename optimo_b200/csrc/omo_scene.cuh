@@ -17,6 +17,7 @@
 #endif
 
 #define OMO_MAXJ OMO_MAX_JOINTS
+#define OMO_MAX_PEERS 16   // ranks of one omo_peer_gather (GPUs of one NVLink / NVSwitch domain)
 #define OMO_NT 128   // threads per block (compile-time: every stack / exchange access gets an immediate offset)
 // OMO_SUB (scene-specialised kernels): (candidate, tile) work items fused into one thread block, each on its own
 // OMO_NT threads and its own slice of dynamic shared memory; they only share the block barriers -- and therefore
@@ -140,6 +141,8 @@ struct OmoEvalParams {
     double* self_dparam;        // [rows] scratch
     double* self_out;           // [rows] f (rows == 1: f, C, D_param, D_traj), device-visible (mapped host or device memory)
     unsigned* self_counter;     // blocks finished; the last one resets it
+    double* self_done;          // mapped host word the last block sets to self_seq once every output is written (null: none); the
+    double self_seq;            // host spins on it instead of waiting for the stream (a few microseconds per single-candidate call)
     double self_h;
     int self_col_begin, self_rows, self_base_row, self_cyclic, self_D;
 };

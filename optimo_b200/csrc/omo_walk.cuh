@@ -366,6 +366,11 @@ struct Walker {
             if (P.self_rows == 1) { P.self_out[1] = C; P.self_out[2] = Dp; P.self_out[3] = Dt; }
         }
         if (tid == 0) *P.self_counter = 0u;
+        if (P.self_done) {   // outputs first (every writer's fence), then the word the host is spinning on
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) *reinterpret_cast<volatile double*>(P.self_done) = P.self_seq;
+        }
     }
 
     // ---- stack traffic ---------------------------------------------------------------------------------------------

@@ -129,3 +129,42 @@ def test_ui_thread_queries_during_a_solve_are_serialised():
     assert np.array_equal(X0, X1) and np.array_equal(F0, F1)
     assert len(seen) > 3
     assert all(n in (235, 245) and np.isfinite(s) and np.isfinite(t) for n, s, t in seen)   # 235: before the first evaluation (core.h:136-139)
+
+
+def test_peer_gather_between_two_processes_equals_the_whole_batch(tmp_path):
+    """omo_peer_gather_* (include/omo.h): two PROCESSES evaluate the halves of one batch; the kernel that forms f stores it into both
+    ranks' gathered arrays through cudaIpc-mapped peer memory and waits for the other rank's flag. Every rank must end up with the
+    bits a single device computes for the whole batch -- on both halves of the double-buffered array, and with a rank that has no
+    candidates in a call. (One GPU: both ranks share device 0 and time-slice; two or more: one device each.)"""
+    import subprocess
+    import sys
+    n = _n_gpus()
+    B, world = 257, 2
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "peer_gather_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(tmp_path), str(r), str(world), str(r if n >= world else 0), str(B)],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for r in range(world)]
+    logs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        logs.append(out.decode(errors="replace")[-2000:])
+    assert all(p.returncode == 0 for p in procs), logs
+    c = Core(synthetic.stick_240(load_scene("stick-figure")), device=0)
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    eng = c.engine(synced_window=(lo, hi))
+    got = [np.load(os.path.join(str(tmp_path), f"out{r}.npy")) for r in range(world)]
+    for call in range(3):
+        f_all = eng.eval(synthetic.perturbed_candidates(x0, B, first=100 * call))
+        for r in range(world):
+            if call == 2:    # the last rank sent nothing: its slice still holds call 0's values (same half of the array)
+                from optimo_b200.core import shard_range
+                b0, nb = shard_range(B, world - 1, world)
+                assert np.array_equal(got[r][call][:b0], f_all[:b0])
+                assert np.array_equal(got[r][call][b0:], got[r][0][b0:])
+            else:
+                assert np.array_equal(got[r][call], f_all), (call, r)
