@@ -24,6 +24,14 @@
 #include "omo_kernels.cuh"
 #include "omo_rnea_z.cuh"
 
+// OMO_PLAN = 1: staged curves whose lanes work on their own samples (no sorted work lists) find their segment through per-channel
+// thresholds in sample-index space (eval_channels_planned); 0: through five FP64 compares per curve and sample (eval_channels_staged).
+// Same results. The generator sets it per scene (omo_jit.hpp: plan_enabled) and reserves the plan area accordingly.
+#ifndef OMO_PLAN
+#define OMO_PLAN 0
+#endif
+#define OMO_PLAN_PAD 16   // plan area rounded up to 16 words = 128 bytes (omo_jit.hpp: place_slots reserves the same)
+
 namespace omo {
 
 // NREG > 0 (scene-specialised kernels only): stack slots numbered 256 + r live in the per-thread array rs[r][] instead of
@@ -78,6 +86,7 @@ struct Walker {
     int* wbase;                       //           [n_keyed] chain position of each keyed channel's first staged record
     int *wcn, *wrow;                  //           [n_keyed] control points / exchange row of each keyed channel (sorted work lists: per-lane lookups)
     double* wts;                      //           [NT] the sample times of the block's window
+    unsigned long long* wplan;        //           [warp][SEGG] segment-search plan of the group being solved (eval_channels_planned)
     int perm_cursor;                  //           entries of the tile's sorted list consumed by the groups solved so far
     int perm_staged;                  //           ... and staged so far (the list of a group travels with its segment records)
     unsigned short* wpm;              //           staged slices of the sorted list, [buf][ceil(SEGG / 3) * 3 * NT]
@@ -166,11 +175,13 @@ struct Walker {
             seg0 = nullptr;
             sgc = P.seg + (size_t)cand * P.n_cp * OMO_SEGD;
             double* tail = stk0 + (size_t)n_smem_slots * ((CPT ? 1 : OMO_SLOT) * NT);
-            // [wbase | wcn | wrow : n_keyed ints each][wts : NT doubles][staging buffers]
-            const int wb_doubles = ((3 * S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double) + NT;
+            // [wbase | wcn | wrow : n_keyed ints each][wts : NT doubles][wplan : SEGG words per warp][staging buffers]
+            constexpr int kPlanWords = OMO_PLAN != 0 ? (((NT / 32) * SEGG + OMO_PLAN_PAD - 1) / OMO_PLAN_PAD) * OMO_PLAN_PAD : 0;   // whole 128-byte lines
+            const int wb_doubles = ((3 * S.n_keyed * (int)sizeof(int) + 15) & ~15) / (int)sizeof(double) + NT + kPlanWords;
             double* const area = stage_in_stack ? stk0 : tail;
             wbase = reinterpret_cast<int*>(area); wcn = wbase + S.n_keyed; wrow = wcn + S.n_keyed;
-            wts = area + (wb_doubles - NT);
+            wts = area + (wb_doubles - NT - kPlanWords);
+            wplan = reinterpret_cast<unsigned long long*>(wts + NT);
             wsb = area + wb_doubles;
             wpm = reinterpret_cast<unsigned short*>(wsb + (size_t)(S.n_groups > 1 ? 2 : 1) * SEGG * OMO_SEGW * OMO_SEGD);
             perm_cursor = 0; perm_staged = 0;
@@ -532,6 +543,38 @@ struct Walker {
         if (SEGG > 0 && !SELF) asm volatile("cp.async.wait_all;" ::: "memory");
     }
 
+    // The segment-search plan of the nch channels grp_list[g0 ..] staged in buffer buf (eval_channels_planned), built by every warp
+    // for itself -- 5 thresholds per channel, one 7-step search over the window's sample times each, spread over the lanes -- so that
+    // no block-wide barrier is needed between the staging of a group and its solve.
+    __device__ __forceinline__ void plan_build(const int buf, const int g0, const int nch)
+    {
+        unsigned char* __restrict__ pl = reinterpret_cast<unsigned char*>(wplan + (tid >> 5) * SEGG);
+#pragma unroll 1
+        for (int it = tid & 31; it < nch * 5; it += 32) {
+            const int lc = it / 5, j = it - lc * 5;
+            const int n = wcn[g0 + lc], nvalid = min(OMO_SEGW, n - wbase[g0 + lc]);
+            const double* __restrict__ rec = wsb + (size_t)((buf * SEGG + lc) * OMO_SEGW) * OMO_SEGD;
+            int th = 128;                                   // never: no record j - 1 in the window
+            if (j - 1 < nvalid && nvalid >= 1) {
+                const double T = (j == 0) ? rec[0] : rec[(j - 1) * OMO_SEGD + 1];   // the key opening record 0 / closing record j - 1
+                int lo = 0, hi = NT;                        // th = number of window samples with !(T <= t): the times ascend
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (!(T <= wts[mid])) lo = mid + 1; else hi = mid;
+                }
+                th = lo;
+            }
+            // byte 4 = th_in (j == 0), bytes 0-3 = th_0..3 (j = 1..4)
+            pl[lc * 8 + (j == 0 ? 4 : j - 1)] = (unsigned char)th;
+            if (j == 0) {
+                pl[lc * 8 + 5] = (unsigned char)max(nvalid, 0);
+                pl[lc * 8 + 6] = (unsigned char)((n < 2 ? 1 : 0) | (n - wbase[g0 + lc] > OMO_SEGW ? 2 : 0));
+                pl[lc * 8 + 7] = 0;
+            }
+        }
+        __syncwarp();
+    }
+
     // K (<= 3) keyed joint channels (entries i0.. of grp_list, rows lc0.. of staging buffer buf) sampled in lockstep from
     // the staged records into the exchange rows
     template <int K>
@@ -562,6 +605,14 @@ struct Walker {
             double tk[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) tk[k] = t;
+            if constexpr (OMO_PLAN != 0 && !SELF) {
+                unsigned long long plan[K];
+                int sik[K];
+                const unsigned long long* __restrict__ wp = wplan + (tid >> 5) * SEGG + lc0;
+#pragma unroll
+                for (int k = 0; k < K; ++k) { plan[k] = wp[k]; sik[k] = idx; }
+                eval_channels_planned<K, COUNT>(sk, plan, sik, tk, val, fb, eb, en);
+            } else
             eval_channels_staged<K, COUNT>(sk, nn, base, tk, val, fb, eb, en);
             if (fb) {   // this thread's segment lies beyond the staged window (keys denser than OMO_SEGW per block)
 #pragma unroll
@@ -681,6 +732,8 @@ struct Walker {
                 tk[k] = wts[si[k]];
             }
             unsigned fb = 0, eb = 0, en = 0;
+            // (the thresholds of eval_channels_planned do not pay here: every lane is on another channel, so the plan words are per-lane
+            // loads like the records, and the slot's byte pattern has to be made per item -- measured on stick240: 0.8776 -> 0.8848 ms)
             eval_channels_staged<3, COUNT>(sk, nn, base, tk, val, fb, eb, en);
             if (fb) {   // the item's segment lies beyond the staged window (keys denser than OMO_SEGW per block)
 #pragma unroll
@@ -702,6 +755,7 @@ struct Walker {
     {
         const OmoDevScene& S = c_scene;
         if (SEGG > 0 && !SELF && !COUNT && P.perm != nullptr && sorted) { curve_group_sorted(buf, g0, n3 + (REM > 0 ? 1 : 0)); return; }
+        if (OMO_PLAN != 0 && SEGG > 0 && !SELF && sorted) plan_build(buf, g0, 3 * n3 + REM);
 #pragma unroll 1
         for (int c = 0; c < n3; ++c) {
             const int i0 = g0 + 3 * c;
