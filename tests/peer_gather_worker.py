@@ -1,6 +1,7 @@
 """One rank of tests/test_multi_gpu.py::test_peer_gather_*: evaluates its slice of a batch through omo_peer_gather_eval and writes
 the gathered f of every call to <dir>/out<rank>.npy. Handles travel through files in <dir> (the test needs no torch).
-    python peer_gather_worker.py <dir> <rank> <world> <device> <B>"""
+    python peer_gather_worker.py <dir> <rank> <world> <device> <B> [absent]
+With `absent`, the last rank connects and then never evaluates: the other ranks' waits must time out with an error, not hang."""
 import os
 import sys
 import time
@@ -14,6 +15,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     d, rank, world, device, B = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
+    absent = len(sys.argv) > 6 and sys.argv[6] == "absent"
     from conftest import load_scene
     from optimo_b200 import synthetic
     from optimo_b200.core import Core, PeerGather, shard_range
@@ -40,6 +42,32 @@ def main():
     eng = c.engine(synced_window=(lo, hi))
     eng.set_batch_hint(B)                      # the kernel the WHOLE batch gets, whatever this rank's share
     pg = PeerGather(eng, rank, world, B, exchange)
+    if absent:
+        from optimo_b200.core import EngineError
+        if rank == world - 1:                  # mapped, never delivers; stays alive until the others have given up
+            t0 = time.time()
+            while not all(os.path.exists(os.path.join(d, f"gave_up{r}")) for r in range(world - 1)) and time.time() - t0 < 60:
+                time.sleep(0.05)
+            pg.close()
+            return
+        X = synthetic.perturbed_candidates(x0, B)
+        b0, nb = shard_range(B, rank, world)
+        dX = eng.device_alloc(8 * max(nb, 1) * x0.size)
+        eng.h2d(dX, X[b0:b0 + nb])
+        t0 = time.time()
+        try:
+            pg.eval(dX, nb, b0, sync=True)
+            outcome = "returned without an error"
+        except EngineError as e:
+            outcome = f"error after {time.time() - t0:.2f} s: {e}"
+        with open(os.path.join(d, f"gave_up{rank}"), "w") as fh:
+            fh.write(outcome)
+        # the context is still usable: an ordinary evaluation of the same rows
+        f = eng.eval(X[b0:b0 + nb])
+        np.save(os.path.join(d, f"after{rank}.npy"), f)
+        eng.device_free(dX)
+        pg.close()
+        return
     results = []
     for call in range(3):                      # three calls: both halves of the gathered array, and the first one again
         X = synthetic.perturbed_candidates(x0, B, first=100 * call)

@@ -168,3 +168,37 @@ def test_peer_gather_between_two_processes_equals_the_whole_batch(tmp_path):
                 assert np.array_equal(got[r][call][b0:], got[r][0][b0:])
             else:
                 assert np.array_equal(got[r][call], f_all), (call, r)
+
+
+def test_peer_gather_wait_times_out_when_a_rank_never_delivers(tmp_path):
+    """A rank that maps its peers and then never evaluates (a crashed process, seen from the others) must not hang the GPU: the
+    waiting kernel gives up after ~2 s, the call returns OMO_NCCL_ERROR, and the context keeps working."""
+    import subprocess
+    import sys
+    n = _n_gpus()
+    B, world = 64, 2
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "peer_gather_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(tmp_path), str(r), str(world), str(r if n >= world else 0), str(B), "absent"],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for r in range(world)]
+    logs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=180)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        logs.append(out.decode(errors="replace")[-2000:])
+    assert all(p.returncode == 0 for p in procs), logs
+    with open(os.path.join(str(tmp_path), "gave_up0")) as fh:
+        outcome = fh.read()
+    assert outcome.startswith("error after") and "status 3" in outcome and "did not arrive" in outcome, outcome
+    assert float(outcome.split()[2]) < 30.0, outcome
+    c = Core(synthetic.stick_240(load_scene("stick-figure")), device=0)
+    x0 = c.GetDescriptor()
+    lo, hi = c.window
+    eng = c.engine(synced_window=(lo, hi))
+    eng.set_batch_hint(B)
+    from optimo_b200.core import shard_range
+    b0, nb = shard_range(B, 0, world)
+    assert np.array_equal(np.load(os.path.join(str(tmp_path), "after0.npy")), eng.eval(synthetic.perturbed_candidates(x0, B)[b0:b0 + nb]))
