@@ -156,6 +156,7 @@ struct omo_ctx {
     int *d_sub_end = nullptr, *d_pos_of_cp = nullptr, *d_ci_of_pos = nullptr, *d_adj_m = nullptr;
     double *d_adj_L = nullptr, *d_adj_G = nullptr, *d_adj_contrib = nullptr, *d_adj_gfull = nullptr, *d_adj_gout = nullptr, *d_oroot = nullptr;
     size_t adj_cap = 0; int adj_F_cap = 0; int adj_max_sub = 0;
+    double* d_adj_ws = nullptr; size_t adj_ws_cap = 0, adj_L_cap = 0; int adj_mode = -1;   // 0 forward, 1 reverse, 2 by size (OMO_ADJ_MODE)
     unsigned long long adj_calls = 0;
 
     // omo_peer_gather_eval in flight: the finish step of the batch launches is the fused finish + peer exchange kernel
@@ -1275,7 +1276,7 @@ void omo_destroy(omo_ctx* ctx)
     if (ctx->d_inv_free) cudaFree(ctx->d_inv_free);
     if (ctx->d_single) cudaFree(ctx->d_single);
     { void* ap[] = {ctx->d_sub_end, ctx->d_pos_of_cp, ctx->d_ci_of_pos, ctx->d_adj_m, ctx->d_adj_L, ctx->d_adj_G, ctx->d_adj_contrib, ctx->d_adj_gfull,
-                    ctx->d_adj_gout, ctx->d_oroot};
+                    ctx->d_adj_gout, ctx->d_oroot, ctx->d_adj_ws};
       for (void* q : ap) if (q) cudaFree(q); }
     if (ctx->d_perm) cudaFree(ctx->d_perm);
     if (ctx->d_self_dparam) cudaFree(ctx->d_self_dparam);
@@ -1795,8 +1796,24 @@ omo_status omo_eval_grad_analytic(omo_ctx* ctx, const double* x, const int* free
         OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // the vectors above are locals
     }
     const size_t cells = (size_t)std::max(nk, 1) * N;
+    // Reverse mode (one thread per sample, O(1) passes over the tree) or forward mode (one thread per (sample, channel, kind), each a
+    // restricted dual-number pass)? Forward mode's many short threads win while they do not fill the GPU -- measured on B200:
+    // stick-figure 216 us against 267, fox-tail 191 against 275 -- reverse mode as soon as they would: the 64-joint x 2000-frame tree
+    // (5.7 M tangent threads) 35.3 -> 3.96 ms. OMO_ADJ_MODE=forward / reverse forces either.
+    if (ctx->adj_mode < 0) { const char* e = std::getenv("OMO_ADJ_MODE"); ctx->adj_mode = !e ? 2 : (std::strcmp(e, "forward") == 0 ? 0 : (std::strcmp(e, "reverse") == 0 ? 1 : 2)); }
+    const bool reverse = ctx->adj_mode == 1 || (ctx->adj_mode == 2 && 3LL * nk * N >= 200000LL);
+    const bool traj_on = ctx->w_traj != 0.0;
+    const size_t L_cells = 3 * (reverse ? (size_t)3 * J * N : cells);
+    if (L_cells > ctx->adj_L_cap) {
+        if ((st = dev_alloc(ctx, &ctx->d_adj_L, L_cells)) != OMO_OK) return st;
+        ctx->adj_L_cap = L_cells;
+    }
+    const size_t ws_cells = reverse ? (size_t)J * (traj_on ? omo_ad::kRevFieldsTraj : omo_ad::kRevFields) * N : 0;
+    if (ws_cells > ctx->adj_ws_cap) {
+        if ((st = dev_alloc(ctx, &ctx->d_adj_ws, ws_cells)) != OMO_OK) return st;
+        ctx->adj_ws_cap = ws_cells;
+    }
     if (cells > ctx->adj_cap) {
-        if ((st = dev_alloc(ctx, &ctx->d_adj_L, 3 * cells)) != OMO_OK) return st;
         if ((st = dev_alloc(ctx, &ctx->d_adj_G, cells)) != OMO_OK) return st;
         if ((st = dev_alloc(ctx, &ctx->d_adj_contrib, 10 * cells)) != OMO_OK) return st;
         if ((st = dev_alloc(ctx, &ctx->d_adj_m, cells)) != OMO_OK) return st;
@@ -1827,14 +1844,22 @@ omo_status omo_eval_grad_analytic(omo_ctx* ctx, const double* x, const int* free
     A.N_s = N; A.n_keyed = nk; A.n_cp = ctx->n_cp; A.D = ctx->D; A.cyclic = ctx->cyclic;
     A.x = ctx->d_X; A.cp_of_pos = ctx->d_cp_of_pos; A.first_of_pos = ctx->d_first_of_pos; A.last_of_pos = ctx->d_last_of_pos;
     A.pos_of_cp = ctx->d_pos_of_cp; A.ci_of_pos = ctx->d_ci_of_pos;
+    A.L_rows = reverse ? 3 * J : nk; A.L_by_channel = reverse ? 1 : 0; A.ws = ctx->d_adj_ws;
     A.L = ctx->d_adj_L; A.G = ctx->d_adj_G; A.contrib = ctx->d_adj_contrib; A.seg_m = ctx->d_adj_m; A.gfull = ctx->d_adj_gfull;
     A.free_idx = ctx->d_free; A.F = F; A.x0 = ctx->d_x0; A.wparam = ctx->d_wparam; A.gout = ctx->d_adj_gout;
     if (nk > 0) {
-        const long long nt = 3LL * nk * N;
-        const unsigned gb = (unsigned)((nt + 127) / 128);
-        if (ctx->adj_max_sub <= 16) omo::adj_tangent_kernel<16><<<gb, 128, 0, ctx->stream>>>(A);
-        else if (ctx->adj_max_sub <= 64) omo::adj_tangent_kernel<64><<<gb, 128, 0, ctx->stream>>>(A);
-        else omo::adj_tangent_kernel<OMO_MAX_JOINTS><<<gb, 128, 0, ctx->stream>>>(A);
+        if (reverse) {
+            // one thread per sample: all 3 x 3J partials from O(1) passes over the tree
+            const unsigned gr = (unsigned)((N + 127) / 128);
+            if (traj_on) omo::adj_reverse_kernel<true><<<gr, 128, 0, ctx->stream>>>(A);
+            else omo::adj_reverse_kernel<false><<<gr, 128, 0, ctx->stream>>>(A);
+        } else {
+            const long long nt = 3LL * nk * N;
+            const unsigned gb = (unsigned)((nt + 127) / 128);
+            if (ctx->adj_max_sub <= 16) omo::adj_tangent_kernel<16><<<gb, 128, 0, ctx->stream>>>(A);
+            else if (ctx->adj_max_sub <= 64) omo::adj_tangent_kernel<64><<<gb, 128, 0, ctx->stream>>>(A);
+            else omo::adj_tangent_kernel<OMO_MAX_JOINTS><<<gb, 128, 0, ctx->stream>>>(A);
+        }
         OMO_CUDA(cudaGetLastError());
         const unsigned gc = (unsigned)((cells + 127) / 128);
         omo::adj_stencil_kernel<<<gc, 128, 0, ctx->stream>>>(A);

@@ -276,6 +276,237 @@ OMO_HD double sample_tangent(const OmoDevScene& S, const int* sub_end, const int
     return w_cost * dt * dcost + (traj ? w_traj * dt * dtraj : 0.0);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------------
+// REVERSE mode: d(cost of one sample) / d(q, qd, qdd) of EVERY joint from one forward sweep, one backward sweep and their adjoints
+// -- O(1) RNEA passes per sample where sample_tangent pays one restricted pass per (channel, kind). Same cost function:
+//     cost = w_cost dt sum_{k >= 1} |tau_k|^2 + w_traj dt sum_k |p_k - p0_k|^2.
+// Adjoint rules used throughout (bars = d cost / d .):   y = a x b:  abar += b x ybar,  bbar += ybar x a;
+//     y = E x:  xbar += E^T ybar,  Ebar += ybar x^T;      y = E^T x:  xbar += E ybar,  Ebar += x ybar^T;      y = M x, M symmetric
+//     (the spatial inertia of rbi_mul):  xbar += M ybar.
+// Order: (A) adjoint of the force fold-back, parents before children: tau_k = S_k^T F_k, F_parent += X_k^T F_k give
+//     Fbar_k = S_k taubar_k + X_k Fbar_parent (+ the E, s, c bars of S_k and X_k); (B) adjoint of the forward sweep, children before
+//     parents: forward_body's outputs (v, a, f) back to (vp, ap, qd, qdd, E, s, c); (C) with w_traj, the forward kinematics:
+//     p_k = L_parent o_k + p_parent, L_k = L_parent R_k.
+// Work memory: NF doubles per body in `ws`, field f of body k at ws[(k * NF + f) * stride] (stride = number of samples on the
+// GPU, where consecutive threads are consecutive samples; 1 on the host).
+// ---------------------------------------------------------------------------------------------------------------------------
+constexpr int kRevFields = 36;        // v 0-5, a 6-11, F (then Fbar) 12-17, sin/cos 18-23, vbar 24-29, abar 30-35
+constexpr int kRevFieldsTraj = 60;    // + L 36-44, Lbar 45-53, p 54-56, pbar collected from the children 57-59
+
+struct Rev3 { double x, y, z; };
+OMO_HD Rev3 rcross(const Rev3& a, const Rev3& b) { return Rev3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+OMO_HD Rev3 radd(const Rev3& a, const Rev3& b) { return Rev3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+OMO_HD Rev3 rmul(const double (&e)[9], const Rev3& v) { return Rev3{e[0] * v.x + e[1] * v.y + e[2] * v.z, e[3] * v.x + e[4] * v.y + e[5] * v.z, e[6] * v.x + e[7] * v.y + e[8] * v.z}; }
+OMO_HD Rev3 rmulT(const double (&e)[9], const Rev3& v) { return Rev3{e[0] * v.x + e[3] * v.y + e[6] * v.z, e[1] * v.x + e[4] * v.y + e[7] * v.z, e[2] * v.x + e[5] * v.y + e[8] * v.z}; }
+// Ebar += y x^T
+OMO_HD void router(double (&eb)[9], const Rev3& y, const Rev3& x)
+{
+    eb[0] += y.x * x.x; eb[1] += y.x * x.y; eb[2] += y.x * x.z;
+    eb[3] += y.y * x.x; eb[4] += y.y * x.y; eb[5] += y.y * x.z;
+    eb[6] += y.z * x.x; eb[7] += y.z * x.y; eb[8] += y.z * x.z;
+}
+
+template <bool TRAJ>
+OMO_HD void sample_reverse(const OmoDevScene& S, const double* q, const double* qd, const double* qdd, const double w_cost, const double w_traj,
+                           const double dt, const double* p0, const long long p0_stride, const double* root_e, const bool interior, double* ws,
+                           const long long stride, double* gq, double* gqd, double* gqdd, const long long gstride)
+{
+    constexpr int NF = TRAJ ? kRevFieldsTraj : kRevFields;
+    const int J = S.J;
+#define OMO_WS(k, f) ws[((long long)(k) * NF + (f)) * stride]
+    auto ld3 = [&](const int k, const int f) { return Rev3{OMO_WS(k, f), OMO_WS(k, f + 1), OMO_WS(k, f + 2)}; };
+    auto st3 = [&](const int k, const int f, const Rev3& v) { OMO_WS(k, f) = v.x; OMO_WS(k, f + 1) = v.y; OMO_WS(k, f + 2) = v.z; };
+    auto ld6 = [&](const int k, const int f) { V6<double> v; v.w0 = OMO_WS(k, f); v.w1 = OMO_WS(k, f + 1); v.w2 = OMO_WS(k, f + 2); v.l0 = OMO_WS(k, f + 3); v.l1 = OMO_WS(k, f + 4); v.l2 = OMO_WS(k, f + 5); return v; };
+    auto st6 = [&](const int k, const int f, const V6<double>& v) { OMO_WS(k, f) = v.w0; OMO_WS(k, f + 1) = v.w1; OMO_WS(k, f + 2) = v.w2; OMO_WS(k, f + 3) = v.l0; OMO_WS(k, f + 4) = v.l1; OMO_WS(k, f + 5) = v.l2; };
+    const double wc2 = 2.0 * w_cost * dt, wt2 = 2.0 * w_traj * dt;
+    // ---- primal: forward sweep (v, a, own force), forward kinematics, force fold-back ---------------------------------------
+    {
+        V6<double> z; zero(z);
+        V6<double> v0 = z, a0 = z;
+        if (interior) { v0.l0 = S.root_qd[0]; v0.l1 = S.root_qd[1]; v0.l2 = S.root_qd[2]; a0.l0 = S.root_qdd[0]; a0.l1 = S.root_qdd[1]; a0.l2 = S.root_qdd[2]; }
+        st6(0, 0, v0); st6(0, 6, a0); st6(0, 12, z); st6(0, 24, z); st6(0, 30, z);
+        if (TRAJ) {
+            double s0, c0, s1, c1, s2, c2, L0[9];
+            sincos_of(root_e[0], s0, c0); sincos_of(root_e[1], s1, c1); sincos_of(root_e[2], s2, c2);
+            local_rotation(s0, c0, s1, c1, s2, c2, L0);
+            for (int c = 0; c < 9; ++c) { OMO_WS(0, 36 + c) = L0[c]; OMO_WS(0, 45 + c) = 0.0; }
+            for (int c = 0; c < 3; ++c) { OMO_WS(0, 54 + c) = S.offset[0][c]; OMO_WS(0, 57 + c) = 0.0; }
+        }
+    }
+    for (int k = 1; k < J; ++k) {
+        const int p = S.parent[k];
+        double s0, c0, s1, c1, s2, c2, e[9];
+        sincos_of(q[3 * k], s0, c0); sincos_of(q[3 * k + 1], s1, c1); sincos_of(q[3 * k + 2], s2, c2);
+        OMO_WS(k, 18) = s0; OMO_WS(k, 19) = c0; OMO_WS(k, 20) = s1; OMO_WS(k, 21) = c1; OMO_WS(k, 22) = s2; OMO_WS(k, 23) = c2;
+        euler_E(s0, c0, s1, c1, s2, c2, e);
+        const double qdk[3] = {qd[3 * k], qd[3 * k + 1], qd[3 * k + 2]}, qddk[3] = {qdd[3 * k], qdd[3 * k + 1], qdd[3 * k + 2]};
+        V6<double> vk, ak, fk, z; zero(z);
+        forward_body(S.body[k], e, s1, c1, s2, c2, qdk, qddk, ld6(p, 0), ld6(p, 6), vk, ak, fk);
+        st6(k, 0, vk); st6(k, 6, ak); st6(k, 12, fk); st6(k, 24, z); st6(k, 30, z);
+        if (TRAJ) {
+            double Lp[9], R[9];
+            for (int c = 0; c < 9; ++c) Lp[c] = OMO_WS(p, 36 + c);
+            const Rev3 o{S.offset[k][0], S.offset[k][1], S.offset[k][2]};
+            const Rev3 pk = radd(rmul(Lp, o), ld3(p, 54));
+            st3(k, 54, pk); st3(k, 57, Rev3{0.0, 0.0, 0.0});
+            local_rotation(s0, c0, s1, c1, s2, c2, R);
+            for (int r = 0; r < 3; ++r)
+                for (int c = 0; c < 3; ++c) { OMO_WS(k, 36 + 3 * r + c) = Lp[3 * r] * R[c] + Lp[3 * r + 1] * R[3 + c] + Lp[3 * r + 2] * R[6 + c]; OMO_WS(k, 45 + 3 * r + c) = 0.0; }
+        }
+    }
+    for (int k = J - 1; k >= 1; --k) {   // F_parent += X_k^T F_k (children before parents); the root's own force is never used
+        const int p = S.parent[k];
+        if (p <= 0) continue;
+        double e[9];
+        euler_E(OMO_WS(k, 18), OMO_WS(k, 19), OMO_WS(k, 20), OMO_WS(k, 21), OMO_WS(k, 22), OMO_WS(k, 23), e);
+        V6<double> g;
+        double t[3];
+        backward_body(S.body[k].r[0], S.body[k].r[1], S.body[k].r[2], e, (double)OMO_WS(k, 20), (double)OMO_WS(k, 22), (double)OMO_WS(k, 23), ld6(k, 12), g, t);
+        V6<double> Fp = ld6(p, 12);
+        add_to(Fp, g);
+        st6(p, 12, Fp);
+    }
+    // ---- (A) adjoint of the fold-back, parents before children: slot F becomes Fbar; the E / s / c bars go straight into gq --------
+    for (int k = 1; k < J; ++k) {
+        const int p = S.parent[k];
+        const double s0 = OMO_WS(k, 18), c0 = OMO_WS(k, 19), s1 = OMO_WS(k, 20), c1 = OMO_WS(k, 21), s2 = OMO_WS(k, 22), c2 = OMO_WS(k, 23);
+        double e[9], eb[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        euler_E(s0, c0, s1, c1, s2, c2, e);
+        const Rev3 Fw = ld3(k, 12), Fl = ld3(k, 15);
+        // tau_k = S^T F.w (backward_body), taubar = 2 w dt tau
+        const Rev3 tb{wc2 * (e[0] * Fw.x + e[3] * Fw.y + s1 * Fw.z), wc2 * (s2 * Fw.x + c2 * Fw.y), wc2 * Fw.z};
+        Rev3 gw{0, 0, 0}, gl{0, 0, 0};
+        if (p > 0) { gw = ld3(p, 12); gl = ld3(p, 15); }        // Fbar of the parent (already converted)
+        const Rev3 r{S.body[k].r[0], S.body[k].r[1], S.body[k].r[2]};
+        const Rev3 evb = radd(gl, rcross(gw, r));                // e_vec = E^T F.l, g.w = E^T F.w + r x e_vec, g.l = e_vec
+        const Rev3 Fbw = radd(Rev3{e[0] * tb.x + s2 * tb.y, e[3] * tb.x + c2 * tb.y, s1 * tb.x + tb.z}, rmul(e, gw));
+        const Rev3 Fbl = rmul(e, evb);
+        router(eb, Fw, gw); router(eb, Fl, evb);
+        double s1b = Fw.z * tb.x, s2b = Fw.x * tb.y, c2b = Fw.y * tb.y, s0b = 0.0, c0b = 0.0, c1b = 0.0;
+        eb[0] += Fw.x * tb.x; eb[3] += Fw.y * tb.x;
+        st3(k, 12, Fbw); st3(k, 15, Fbl);
+        // euler_E adjoint
+        c2b += eb[0] * c1 + eb[1] * s1 * s0 - eb[2] * s1 * c0 + eb[4] * c0 + eb[5] * s0;
+        c1b += eb[0] * c2 - eb[3] * s2 - eb[7] * s0 + eb[8] * c0;
+        s1b += eb[1] * c2 * s0 - eb[2] * c2 * c0 - eb[4] * s2 * s0 + eb[5] * s2 * c0 + eb[6];
+        s0b += eb[1] * c2 * s1 + eb[2] * s2 - eb[4] * s2 * s1 + eb[5] * c2 - eb[7] * c1;
+        s2b += eb[1] * c0 + eb[2] * s0 - eb[3] * c1 - eb[4] * s1 * s0 + eb[5] * s1 * c0;
+        c0b += eb[1] * s2 - eb[2] * c2 * s1 + eb[4] * c2 + eb[5] * s2 * s1 + eb[8] * c1;
+        gq[(long long)(3 * k) * gstride] = s0b * c0 - c0b * s0;
+        gq[(long long)(3 * k + 1) * gstride] = s1b * c1 - c1b * s1;
+        gq[(long long)(3 * k + 2) * gstride] = s2b * c2 - c2b * s2;
+    }
+    // ---- (B) adjoint of the forward sweep + (C) of the forward kinematics, children before parents ------------------------------
+    for (int k = J - 1; k >= 1; --k) {
+        const int p = S.parent[k];
+        const OmoBody& B = S.body[k];
+        const double s0 = OMO_WS(k, 18), c0 = OMO_WS(k, 19), s1 = OMO_WS(k, 20), c1 = OMO_WS(k, 21), s2 = OMO_WS(k, 22), c2 = OMO_WS(k, 23);
+        double e[9], eb[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        euler_E(s0, c0, s1, c1, s2, c2, e);
+        const Rev3 r{B.r[0], B.r[1], B.r[2]};
+        const Rev3 w = ld3(k, 0), l = ld3(k, 3);
+        const Rev3 wp = ld3(p, 0), lp = ld3(p, 3), alp = ld3(p, 6), bep = ld3(p, 9);
+        const Rev3 qdk{qd[3 * k], qd[3 * k + 1], qd[3 * k + 2]}, qddk{qdd[3 * k], qdd[3 * k + 1], qdd[3 * k + 2]};
+        const Rev3 vJ{e[0] * qdk.x + s2 * qdk.y, e[3] * qdk.x + c2 * qdk.y, s1 * qdk.x + qdk.z};
+        const Rev3 xv = radd(lp, rcross(wp, r)), xa = radd(bep, rcross(alp, r));
+        V6<double> vk, Iv; vk.w0 = w.x; vk.w1 = w.y; vk.w2 = w.z; vk.l0 = l.x; vk.l1 = l.y; vk.l2 = l.z;
+        rbi_mul(B, vk, Iv);
+        const Rev3 Ivw{Iv.w0, Iv.w1, Iv.w2}, Ivl{Iv.l0, Iv.l1, Iv.l2};
+        const Rev3 fbw = ld3(k, 12), fbl = ld3(k, 15);          // fbar = Fbar_k
+        // f = I a + v x* (I v)
+        Rev3 wb = radd(ld3(k, 24), radd(rcross(Ivw, fbw), rcross(Ivl, fbl)));
+        Rev3 lb = radd(ld3(k, 27), rcross(Ivl, fbw));
+        V6<double> Ivb, Iab, t6;
+        { const Rev3 a1 = rcross(fbw, w), a2 = radd(rcross(fbw, l), rcross(fbl, w)); Ivb.w0 = a1.x; Ivb.w1 = a1.y; Ivb.w2 = a1.z; Ivb.l0 = a2.x; Ivb.l1 = a2.y; Ivb.l2 = a2.z; }
+        rbi_mul(B, Ivb, t6);
+        wb = radd(wb, Rev3{t6.w0, t6.w1, t6.w2}); lb = radd(lb, Rev3{t6.l0, t6.l1, t6.l2});
+        Iab.w0 = fbw.x; Iab.w1 = fbw.y; Iab.w2 = fbw.z; Iab.l0 = fbl.x; Iab.l1 = fbl.y; Iab.l2 = fbl.z;
+        rbi_mul(B, Iab, t6);
+        const Rev3 alb = radd(ld3(k, 30), Rev3{t6.w0, t6.w1, t6.w2}), beb = radd(ld3(k, 33), Rev3{t6.l0, t6.l1, t6.l2});
+        // a = X ap + S qdd + cJ + v x vJ
+        Rev3 apbw = rmulT(e, alb);
+        router(eb, alb, alp);
+        const Rev3 qddb{e[0] * alb.x + e[3] * alb.y + s1 * alb.z, s2 * alb.x + c2 * alb.y, alb.z};
+        const Rev3 xab = rmulT(e, beb);
+        router(eb, beb, xa);
+        apbw = radd(apbw, rcross(r, xab));
+        wb = radd(wb, rcross(vJ, alb));
+        Rev3 vJb = rcross(alb, w);
+        lb = radd(lb, rcross(vJ, beb));
+        vJb = radd(vJb, rcross(beb, l));
+        // v = X vp + vJ
+        Rev3 vpbw = rmulT(e, wb);
+        router(eb, wb, wp);
+        vJb = radd(vJb, wb);
+        const Rev3 xvb = rmulT(e, lb);
+        router(eb, lb, xv);
+        vpbw = radd(vpbw, rcross(r, xvb));
+        // vJ = S qd, S qdd inside a
+        Rev3 qdb{e[0] * vJb.x + e[3] * vJb.y + s1 * vJb.z, s2 * vJb.x + c2 * vJb.y, vJb.z};
+        double e0b = alb.x * qddk.x + vJb.x * qdk.x, e3b = alb.y * qddk.x + vJb.y * qdk.x, s1b = alb.z * qddk.x + vJb.z * qdk.x;
+        double s2b = alb.x * qddk.y + vJb.x * qdk.y, c2b = alb.y * qddk.y + vJb.y * qdk.y, s0b = 0.0, c0b = 0.0, c1b = 0.0;
+        // cJ (cJbar = alb)
+        {
+            const double q20 = qdk.z * qdk.x, q10 = qdk.y * qdk.x, q21 = qdk.z * qdk.y;
+            e3b += alb.x * q20; e0b -= alb.y * q20;
+            const double q20b = alb.x * e[3] - alb.y * e[0];
+            const double q10b = -alb.x * c2 * s1 + alb.y * s2 * s1 + alb.z * c1;
+            const double q21b = alb.x * c2 - alb.y * s2;
+            c2b += alb.x * (-s1 * q10 + q21);
+            s1b += -alb.x * c2 * q10 + alb.y * s2 * q10;
+            s2b += alb.y * (s1 * q10 - q21);
+            c1b += alb.z * q10;
+            qdb.x += q20b * qdk.z + q10b * qdk.y;
+            qdb.y += q10b * qdk.x + q21b * qdk.z;
+            qdb.z += q20b * qdk.x + q21b * qdk.y;
+        }
+        eb[0] += e0b; eb[3] += e3b;
+        // parents collect (the root's state is constant)
+        if (p > 0) {
+            st3(p, 24, radd(ld3(p, 24), vpbw)); st3(p, 27, radd(ld3(p, 27), xvb));
+            st3(p, 30, radd(ld3(p, 30), apbw)); st3(p, 33, radd(ld3(p, 33), xab));
+        }
+        // euler_E adjoint
+        c2b += eb[0] * c1 + eb[1] * s1 * s0 - eb[2] * s1 * c0 + eb[4] * c0 + eb[5] * s0;
+        c1b += eb[0] * c2 - eb[3] * s2 - eb[7] * s0 + eb[8] * c0;
+        s1b += eb[1] * c2 * s0 - eb[2] * c2 * c0 - eb[4] * s2 * s0 + eb[5] * s2 * c0 + eb[6];
+        s0b += eb[1] * c2 * s1 + eb[2] * s2 - eb[4] * s2 * s1 + eb[5] * c2 - eb[7] * c1;
+        s2b += eb[1] * c0 + eb[2] * s0 - eb[3] * c1 - eb[4] * s1 * s0 + eb[5] * s1 * c0;
+        c0b += eb[1] * s2 - eb[2] * c2 * s1 + eb[4] * c2 + eb[5] * s2 * s1 + eb[8] * c1;
+        if (TRAJ) {
+            // p_k = L_p o_k + p_p and L_k = L_p R_k (R_k = Rz Ry Rx of this joint's angles): every child of k has been here already
+            double Lp[9], Lbk[9], R[9], Rb[9];
+            for (int c = 0; c < 9; ++c) { Lp[c] = OMO_WS(p, 36 + c); Lbk[c] = OMO_WS(k, 45 + c); }
+            const Rev3 pk = ld3(k, 54);
+            const Rev3 pb = radd(ld3(k, 57), Rev3{wt2 * (pk.x - p0[(long long)(3 * k) * p0_stride]), wt2 * (pk.y - p0[(long long)(3 * k + 1) * p0_stride]),
+                                                  wt2 * (pk.z - p0[(long long)(3 * k + 2) * p0_stride])});
+            local_rotation(s0, c0, s1, c1, s2, c2, R);
+            for (int m = 0; m < 3; ++m)
+                for (int c = 0; c < 3; ++c) Rb[3 * m + c] = Lp[m] * Lbk[c] + Lp[3 + m] * Lbk[3 + c] + Lp[6 + m] * Lbk[6 + c];
+            if (p > 0) {   // the root's frame and position are constants
+                const double o[3] = {S.offset[k][0], S.offset[k][1], S.offset[k][2]};
+                const double pbv[3] = {pb.x, pb.y, pb.z};
+                for (int rr = 0; rr < 3; ++rr)
+                    for (int m = 0; m < 3; ++m)
+                        OMO_WS(p, 45 + 3 * rr + m) += pbv[rr] * o[m] + Lbk[3 * rr] * R[3 * m] + Lbk[3 * rr + 1] * R[3 * m + 1] + Lbk[3 * rr + 2] * R[3 * m + 2];
+                st3(p, 57, radd(ld3(p, 57), pb));
+            }
+            c2b += Rb[0] * c1 + Rb[1] * s1 * s0 + Rb[2] * s1 * c0 + Rb[4] * c0 - Rb[5] * s0;
+            c1b += Rb[0] * c2 + Rb[3] * s2 + Rb[7] * s0 + Rb[8] * c0;
+            s1b += Rb[1] * c2 * s0 + Rb[2] * c2 * c0 + Rb[4] * s2 * s0 + Rb[5] * s2 * c0 - Rb[6];
+            s0b += Rb[1] * c2 * s1 + Rb[2] * s2 + Rb[4] * s2 * s1 - Rb[5] * c2 + Rb[7] * c1;
+            s2b += -Rb[1] * c0 + Rb[2] * s0 + Rb[3] * c1 + Rb[4] * s1 * s0 + Rb[5] * s1 * c0;
+            c0b += -Rb[1] * s2 + Rb[2] * c2 * s1 + Rb[4] * c2 + Rb[5] * s2 * s1 + Rb[8] * c1;
+        }
+        gq[(long long)(3 * k) * gstride] += s0b * c0 - c0b * s0;
+        gq[(long long)(3 * k + 1) * gstride] += s1b * c1 - c1b * s1;
+        gq[(long long)(3 * k + 2) * gstride] += s2b * c2 - c2b * s2;
+        gqd[(long long)(3 * k) * gstride] = qdb.x; gqd[(long long)(3 * k + 1) * gstride] = qdb.y; gqd[(long long)(3 * k + 2) * gstride] = qdb.z;
+        gqdd[(long long)(3 * k) * gstride] = qddb.x; gqdd[(long long)(3 * k + 1) * gstride] = qddb.y; gqdd[(long long)(3 * k + 2) * gstride] = qddb.z;
+    }
+#undef OMO_WS
+}
+
 // Transposed stencils (core_rbdl.cpp:28-95, SECOND_ORDER_ACCURATE off): coefficient of q[i] in qd[m] / qdd[m], N samples.
 OMO_HD double d1_coef(const int m, const int i, const int N, const double dt)
 {

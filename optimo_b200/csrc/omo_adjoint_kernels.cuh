@@ -21,7 +21,10 @@ struct OmoAdjParams {
     const double* x;               // [D] the evaluated descriptor
     const int *cp_of_pos, *first_of_pos, *last_of_pos, *pos_of_cp, *ci_of_pos;
     // work arrays
-    double* L;                     // [3][n_keyed][N_s]  d cost_i / d (q, qd, qdd)_c at sample i
+    double* L;                     // [3][L_rows][N_s]   d cost_i / d (q, qd, qdd)_c at sample i; rows = keyed channels (forward mode: L_rows =
+                                   //                    n_keyed) or ALL joint channels 3j + axis (reverse mode: L_rows = 3J, L_by_channel = 1)
+    int L_rows, L_by_channel;
+    double* ws;                    // reverse mode: [J][fields][N_s] work memory of omo_ad::sample_reverse
     double* G;                     // [n_keyed][N_s]     d f / d q_c(t_i)
     double* contrib;               // [n_keyed][N_s][10] G times the value's partials w.r.t. the segment's two control points
     int* seg_m;                    // [n_keyed][N_s]     number of keys with time <= t_i
@@ -52,15 +55,32 @@ __global__ void __launch_bounds__(128) adj_tangent_kernel(const OmoAdjParams P)
                                               P.wcost[i], P.p_orig ? P.w_traj : 0.0, P.dt, P.p_orig ? P.p_orig + i : nullptr, P.N_s, re, interior);
 }
 
+// 1'. reverse mode: one thread per sample, every joint channel's three partials from one forward sweep, one fold-back and their
+// adjoints (omo_ad::sample_reverse); consecutive threads are consecutive samples in every array it touches
+template <bool TRAJ>
+__global__ void __launch_bounds__(128) adj_reverse_kernel(const OmoAdjParams P)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.N_s) return;
+    const OmoDevScene& S = c_scene;
+    const size_t dof = (size_t)3 * S.J, N = (size_t)P.N_s;
+    const bool interior = (i >= 2) && (i <= P.N_s - 3);
+    double re[3] = {S.chan_const[0], S.chan_const[1], S.chan_const[2]};
+    if (P.root_e) { re[0] = P.root_e[3 * (size_t)i]; re[1] = P.root_e[3 * (size_t)i + 1]; re[2] = P.root_e[3 * (size_t)i + 2]; }
+    omo_ad::sample_reverse<TRAJ>(S, P.q + i * dof, P.qd + i * dof, P.qdd + i * dof, P.wcost[i], TRAJ ? P.w_traj : 0.0, P.dt, TRAJ ? P.p_orig + i : nullptr,
+                                 (long long)N, re, interior, P.ws + i, (long long)N, P.L + i, P.L + dof * N + i, P.L + 2 * dof * N + i, (long long)N);
+}
+
 // 2. transposed stencils: one thread per (keyed channel, sample)
 __global__ void adj_stencil_kernel(const OmoAdjParams P)
 {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (long long)P.n_keyed * P.N_s) return;
     const int i = (int)(idx % P.N_s), ci = (int)(idx / P.N_s), N = P.N_s;
-    const double* __restrict__ Lq = P.L + (size_t)ci * N;
-    const double* __restrict__ Lv = P.L + ((size_t)P.n_keyed + ci) * N;
-    const double* __restrict__ La = P.L + ((size_t)2 * P.n_keyed + ci) * N;
+    const size_t row = P.L_by_channel ? (size_t)c_scene.grp_list[ci] : (size_t)ci;
+    const double* __restrict__ Lq = P.L + row * N;
+    const double* __restrict__ Lv = P.L + ((size_t)P.L_rows + row) * N;
+    const double* __restrict__ La = P.L + ((size_t)2 * P.L_rows + row) * N;
     double g = Lq[i];
     for (int m = max(i - 2, 0); m <= min(i + 2, N - 1); ++m)
         g += omo_ad::d1_coef(m, i, N, P.dt) * Lv[m] + omo_ad::d2_coef(m, i, N, P.dt) * La[m];

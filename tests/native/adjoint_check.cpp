@@ -66,6 +66,16 @@ double adj_sample_tangent(const void* scene, const int* sub_end, int j, int axis
                                           root_e, interior != 0);
 }
 
+// reverse mode: all 3 x 3J partials of one sample's cost at once (gq, gqd, gqdd: [3J], entries of the root untouched)
+void adj_sample_reverse(const void* scene, const double* q, const double* qd, const double* qdd, double w_cost, double w_traj, double dt, const double* p0,
+                        long long p0_stride, const double* root_e, int interior, double* gq, double* gqd, double* gqdd)
+{
+    const OmoDevScene& S = *static_cast<const OmoDevScene*>(scene);
+    static double ws[OMO_MAX_JOINTS * kRevFieldsTraj];
+    if (w_traj != 0.0) sample_reverse<true>(S, q, qd, qdd, w_cost, w_traj, dt, p0, p0_stride, root_e, interior != 0, ws, 1, gq, gqd, gqdd, 1);
+    else sample_reverse<false>(S, q, qd, qdd, w_cost, 0.0, dt, nullptr, 0, root_e, interior != 0, ws, 1, gq, gqd, gqdd, 1);
+}
+
 double adj_bezier(const double* ps, const double* pe, double ths, double the, double t, double* out10)
 {
     double o[10];

@@ -35,6 +35,8 @@ def adj():
     lib.adj_sample_tangent.restype = C.c_double
     lib.adj_sample_tangent.argtypes = [C.c_void_p, _ip, C.c_int, C.c_int, C.c_int, _dp, _dp, _dp, _dp, C.c_double, C.c_double, C.c_double, _dp, C.c_longlong,
                                        _dp, C.c_int]
+    lib.adj_sample_reverse.restype = None
+    lib.adj_sample_reverse.argtypes = [C.c_void_p, _dp, _dp, _dp, C.c_double, C.c_double, C.c_double, _dp, C.c_longlong, _dp, C.c_int, _dp, _dp, _dp]
     lib.adj_bezier.restype = C.c_double
     lib.adj_bezier.argtypes = [_dp, _dp, C.c_double, C.c_double, C.c_double, _dp]
     lib.adj_d1.restype = C.c_double
@@ -178,3 +180,30 @@ def test_stencil_coefficients_are_the_reference_difference_operators(adj):
         q = rng.standard_normal(n)
         d1, d2 = _reference_stencils(q, 0.2)
         assert np.allclose(D1 @ q, d1, rtol=1e-13, atol=1e-13) and np.allclose(D2 @ q, d2, rtol=1e-13, atol=1e-12), n
+
+
+@pytest.mark.parametrize("name", ["stick-figure", "fox-tail", "conductor", "tree16"])
+@pytest.mark.parametrize("w_traj", [0.0, 12.5])
+def test_reverse_mode_equals_the_forward_mode_tangents_on_every_joint_channel(adj, name, w_traj):
+    """omo_ad::sample_reverse (one forward sweep, one fold-back and their hand-written adjoints: every d cost / d (q, qd, qdd) of a
+    sample at once) against omo_ad::sample_tangent (one dual-number pass per channel and kind, itself checked against central
+    differences above): all 3 x 3(J-1) partials, random states, with and without the trajectory term, chains and trees."""
+    from optimo_b200 import synthetic
+    scene = synthetic.tree_scene(16, 60) if name == "tree16" else load_scene(name)
+    core = Core(scene)
+    table, sub_end = core.debug_scene_table(int(adj.adj_sizeof_scene()))
+    J = core.J
+    rng = np.random.default_rng(11)
+    q, qd, qdd = 0.7 * rng.standard_normal(3 * J), rng.standard_normal(3 * J), 3.0 * rng.standard_normal(3 * J)
+    p0, root_e = rng.standard_normal(3 * J), 0.3 * rng.standard_normal(3)
+    tau = np.zeros(3 * J)
+    adj.adj_sample_cost(table, _p(q), _p(qd), _p(qdd), 0.7, w_traj, 0.2, _p(p0), 1, _p(root_e), 1, _p(tau))
+    g = [np.zeros(3 * J) for _ in range(3)]
+    adj.adj_sample_reverse(table, _p(q), _p(qd), _p(qdd), 0.7, w_traj, 0.2, _p(p0), 1, _p(root_e), 1, _p(g[0]), _p(g[1]), _p(g[2]))
+    scale = max(np.abs(np.concatenate(g)).max(), 1e-300)
+    for j in range(1, J):
+        for axis in range(3):
+            for kind in range(3):
+                t = adj.adj_sample_tangent(table, sub_end.ctypes.data_as(_ip), j, axis, kind, _p(q), _p(qd), _p(qdd), _p(tau), 0.7, w_traj, 0.2, _p(p0), 1,
+                                           _p(root_e), 1)
+                assert abs(g[kind][3 * j + axis] - t) <= 1e-11 * abs(t) + 1e-13 * scale, (j, axis, kind, g[kind][3 * j + axis], t)

@@ -89,3 +89,26 @@ def test_scenes_outside_the_analytic_gradient_fall_back_to_finite_differences():
     f, g, used = s.CalculateAnalyticGradient(*s.window, x, xs)
     f2, g2, _ = s.CalculateGradient(*s.window, x, xs)
     assert not used and f == f2 and np.array_equal(g, g2)
+
+
+@pytest.mark.parametrize("name,w_traj", [("stick-figure", 0.0), ("stick-figure", 12.5), ("fox-tail", 12.5)])
+def test_reverse_mode_kernel_equals_the_forward_mode_kernel(name, w_traj, monkeypatch):
+    """The default (reverse mode: one thread per sample, O(1) passes over the tree) against OMO_ADJ_MODE=forward (one dual-number pass per
+    channel and kind): the same gradient to rounding -- they share every kernel behind the per-sample partials."""
+    from conftest import scene_path
+    from optimo_b200.core import Core
+    grads = {}
+    for mode in ("reverse", "forward"):
+        monkeypatch.setenv("OMO_ADJ_MODE", mode)
+        c = Core(scene_path(name))
+        c.UpdateGlobalWeight(w_traj)
+        x0 = c.GetDescriptor()
+        rng = np.random.default_rng(5)
+        x = x0.copy(); x[2::5] += 0.3 * (rng.random(x.size // 5) - 0.5)
+        lo, hi = c.window
+        f, g, used = c.CalculateAnalyticGradient(lo, hi, x, x0)
+        assert used
+        grads[mode] = (f, g)
+    assert grads["reverse"][0] == grads["forward"][0]
+    gr, gf = grads["reverse"][1], grads["forward"][1]
+    assert np.max(np.abs(gr - gf)) <= 1e-10 * np.max(np.abs(gf)), float(np.max(np.abs(gr - gf)) / np.max(np.abs(gf)))
