@@ -438,7 +438,9 @@ def measure_single(G, W, steps, warmup, dfma_peak, cpu_candidates, full=False, s
         else:
             eng.eval_host_ptr(W.Xp.ctypes.data, B, W.Fp.ctypes.data)     # H2D of X, kernels, D2H of f, all inside
 
-    ms_dev, wall_dev, (k_ms, k_n), launches = G.timed(eng, step_device, steps, warmup, kernel_timing=True)
+    # the step is timed WITHOUT the engine's own kernel-timing events in the stream; the objective kernel's time comes from a second pass
+    ms_dev, wall_dev, _, launches = G.timed(eng, step_device, steps, warmup)
+    _, _, (k_ms, k_n), _ = G.timed(eng, step_device, steps, 1, kernel_timing=True)
     ms_e2e, wall_e2e, _, _ = G.timed(eng, step_e2e, steps, max(warmup, 3))
     f_dev = W.dF.cpu().numpy()
     assert np.array_equal(f_dev, np.asarray(W.Fp)), "device-resident and host-buffer paths disagree"
@@ -694,7 +696,8 @@ def run_multi_gpu(G, args):
     sampler = ClockSampler(G.local) if rank == 0 else None
     if sampler:
         sampler.start()
-    ms_nccl, wall_dev, (k_ms, k_n), launches = G.timed(eng, strong_device, args.steps, args.warmup, kernel_timing=True)
+    ms_nccl, wall_dev, _, launches = G.timed(eng, strong_device, args.steps, args.warmup)
+    _, _, (k_ms, k_n), _ = G.timed(eng, strong_device, args.steps, 1, kernel_timing=True)   # kernel time from a pass of its own: no timing events inside the measured step
     ms_e2e, wall_e2e, _, _ = G.timed(eng, strong_e2e, args.steps, max(args.warmup, 3))
     f_strong = np.concatenate([dAll.cpu().numpy()[r * pad: r * pad + shard_range(B, r, world)[1]] for r in range(world)])
 
@@ -720,7 +723,8 @@ def run_multi_gpu(G, args):
     if int(t_ok.item()) == 1:
         def strong_device_peer():
             pg.eval(dXs.data_ptr(), nb, b0, sync=False)
-        ms_peer, wall_peer, (k_ms_p, k_n_p), launches_p = G.timed(eng, strong_device_peer, args.steps, args.warmup, kernel_timing=True)
+        ms_peer, wall_peer, _, launches_p = G.timed(eng, strong_device_peer, args.steps, args.warmup)
+        _, _, (k_ms_p, k_n_p), _ = G.timed(eng, strong_device_peer, args.steps, 1, kernel_timing=True)
         f_peer = eng.d2h(pg.values(), (B,))
         same = bool(np.array_equal(f_peer, f_strong)) and pg.error() == 0
         t_same = torch.tensor([1 if same else 0], dtype=torch.int32, device="cuda")
