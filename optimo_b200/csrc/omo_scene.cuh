@@ -141,8 +141,6 @@ struct OmoEvalParams {
     double* self_dparam;        // [rows] scratch
     double* self_out;           // [rows] f (rows == 1: f, C, D_param, D_traj), device-visible (mapped host or device memory)
     unsigned* self_counter;     // blocks finished; the last one resets it
-    double* self_done;          // mapped host word the last block sets to self_seq once every output is written (null: none); the
-    double self_seq;            // host spins on it instead of waiting for the stream (a few microseconds per single-candidate call)
     double self_h;
     int self_col_begin, self_rows, self_base_row, self_cyclic, self_D;
 };

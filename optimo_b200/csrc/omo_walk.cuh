@@ -377,11 +377,8 @@ struct Walker {
             if (P.self_rows == 1) { P.self_out[1] = C; P.self_out[2] = Dp; P.self_out[3] = Dt; }
         }
         if (tid == 0) *P.self_counter = 0u;
-        if (P.self_done) {   // outputs first (every writer's fence), then the word the host is spinning on
-            __threadfence_system();
-            __syncthreads();
-            if (tid == 0) *reinterpret_cast<volatile double*>(P.self_done) = P.self_seq;
-        }
+        // (no completion word and no system-scope fence behind the outputs: where they go to mapped host memory the host has filled the
+        // slots with a sentinel and polls until every one of them has been overwritten -- omo.cu: wait_self)
     }
 
     // ---- stack traffic ---------------------------------------------------------------------------------------------
