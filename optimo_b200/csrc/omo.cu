@@ -145,6 +145,7 @@ struct omo_ctx {
     double* d_self_out = nullptr;               // its device alias
     int self_out_cap = 0;
     int self_spin_slots = 0;                    // outputs of the self-preparing launch in flight that the host polls in h_self_out (0: wait on the stream)
+    int self_host_tiles = 0;                    // > 0: single candidate whose tile partials the HOST adds up (slots 4 .. of h_self_out), see launch_self
     int self_spin_mode = -1;                    // OMO_SPIN=0: always wait on the stream
     unsigned long long self_launches = 0;
 
@@ -1039,18 +1040,28 @@ constexpr unsigned long long kSelfSentinel = 0x7ff8dead5e1fbeefull;
 omo_status wait_self(omo_ctx* ctx)
 {
     if (ctx->self_spin_slots > 0) {
-        const int n = ctx->self_spin_slots;
-        ctx->self_spin_slots = 0;
+        const int n = ctx->self_spin_slots, host_tiles = ctx->self_host_tiles;
+        ctx->self_spin_slots = 0; ctx->self_host_tiles = 0;
         const volatile unsigned long long* out = reinterpret_cast<const volatile unsigned long long*>(ctx->h_self_out);
-        int next = 0;    // slots below `next` have arrived
+        int next = host_tiles > 0 ? 4 : 0;    // slots below `next` have arrived
+        auto reduce_on_host = [&]() {
+            // finish_kernel's sums, same order: C and D_traj over the tiles from 0.0 up, then f = C + D_param + D_traj
+            volatile double* h = ctx->h_self_out;
+            double C = 0.0, Dt = 0.0;
+            for (int t = 0; t < host_tiles; ++t) { C = C + h[4 + 2 * t]; Dt = Dt + h[4 + 2 * t + 1]; }
+            double Dp = 0.0;
+            Dp = Dp + h[4 + 2 * host_tiles];
+            const double f = (C + Dp) + Dt;
+            h[0] = f; h[1] = C; h[2] = Dp; h[3] = Dt;
+        };
         for (unsigned spin = 1;; ++spin) {
             while (next < n && out[next] != kSelfSentinel) ++next;
-            if (next == n) return OMO_OK;
+            if (next == n) { if (host_tiles > 0) reduce_on_host(); return OMO_OK; }
             if ((spin & 2047u) == 0u) {
                 const cudaError_t q = cudaStreamQuery(ctx->stream);
                 if (q == cudaSuccess) {
                     while (next < n && out[next] != kSelfSentinel) ++next;
-                    if (next == n) return OMO_OK;
+                    if (next == n) { if (host_tiles > 0) reduce_on_host(); return OMO_OK; }
                     return fail(ctx, OMO_CUDA_ERROR, "self-preparing kernel finished without writing all of its outputs");
                 }
                 if (q != cudaErrorNotReady) { ctx->err = std::string("self-preparing launch: ") + cudaGetErrorString(q); return OMO_CUDA_ERROR; }
@@ -1093,12 +1104,24 @@ omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_ro
     // results into the context's mapped host buffer: the host polls the output slots themselves (wait_self) instead of paying the stream
     // synchronisation's round trip through the driver
     if (ctx->self_spin_mode < 0) { const char* e = std::getenv("OMO_SPIN"); ctx->self_spin_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
-    ctx->self_spin_slots = 0;
+    ctx->self_spin_slots = 0; ctx->self_host_tiles = 0;
     if (out == ctx->d_self_out && ctx->self_spin_mode == 1 && !ctx->timing) {
-        const int n_out = rows == 1 ? 4 : (base_row >= 0 ? rows - 1 : rows);   // what self_finish writes: (f, C, D_param, D_traj) or one f per row
         unsigned long long* slots = reinterpret_cast<unsigned long long*>(ctx->h_self_out);
-        for (int i = 0; i < n_out; ++i) slots[i] = kSelfSentinel;
-        ctx->self_spin_slots = n_out;
+        if (rows == 1 && d_item_map == nullptr && 5 + 2 * plan.n_tiles <= ctx->self_out_cap) {
+            // ONE candidate: every block writes its tile's (C, D_traj) pair -- and the block of tile 0 D_param -- straight into the mapped
+            // buffer (slots 4 .., behind the four result slots), and the host adds them in finish_kernel's order (wait_self). The kernel's
+            // tail -- fence, ticket, barrier, the last block's loads -- is gone from every BOBYQA callback.
+            P.partial = ctx->d_self_out + 4;
+            P.self_dparam = ctx->d_self_out + 4 + 2 * plan.n_tiles;
+            P.self_counter = nullptr;
+            ctx->self_host_tiles = plan.n_tiles;
+            for (int i = 4; i < 5 + 2 * plan.n_tiles; ++i) slots[i] = kSelfSentinel;
+            ctx->self_spin_slots = 5 + 2 * plan.n_tiles;
+        } else {
+            const int n_out = rows == 1 ? 4 : (base_row >= 0 ? rows - 1 : rows);   // what self_finish writes: (f, C, D_param, D_traj) or one f per row
+            for (int i = 0; i < n_out; ++i) slots[i] = kSelfSentinel;
+            ctx->self_spin_slots = n_out;
+        }
     }
     omo_jit::Api& a = omo_jit::api();
     if (k->uploaded_version != ctx->scene_version) {

@@ -350,6 +350,16 @@ struct Walker {
     __device__ __forceinline__ void self_finish()
     {
         __shared__ int last_block;
+        if (P.self_counter == nullptr) {
+            // single candidate with the host as the reducer (omo.cu: launch_self): `partial` and `self_dparam` ARE slots of the mapped host
+            // buffer, the host adds them in finish_kernel's order once they have arrived -- no ticket, no fence, no last block
+            if (tid == 0 && self_books_dparam) {
+                double sum = 0.0;
+                for (int w = 0; w < NT / 32; ++w) sum += self_red[w];
+                P.self_dparam[cand_] = sum;
+            }
+            return;
+        }
         if (tid == 0) {
             if (self_books_dparam) {
                 double sum = 0.0;
