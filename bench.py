@@ -705,17 +705,22 @@ def run_multi_gpu(G, args):
     # NCCL call). Used for the headline when every rank could map its peers and the gathered values equal the NCCL path's bit for bit.
     peer = {"available": False}
     pg = None
+    ok = 1
     try:
         from optimo_b200.core import PeerGather
-
-        def exchange(handle):
-            got = [None] * world
-            dist.all_gather_object(got, handle)
-            return got
-        pg = PeerGather(eng, rank, world, B, exchange)
-        ok = 1
+        pg = PeerGather(eng, rank, world, B)
     except Exception as e:   # noqa: BLE001
         peer["error"] = str(e)[:300]
+        pg, ok = None, 0
+    handles = [None] * world
+    dist.all_gather_object(handles, pg.handle if pg is not None else None)   # every rank takes part, whatever happened above
+    if ok and all(hd is not None for hd in handles):
+        try:
+            pg.connect(handles)
+        except Exception as e:   # noqa: BLE001
+            peer["error"] = str(e)[:300]
+            ok = 0
+    else:
         ok = 0
     t_ok = torch.tensor([ok], dtype=torch.int32, device="cuda")
     dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)

@@ -405,16 +405,23 @@ class PeerGather:
     rank order]` is the caller's transport (torch.distributed.all_gather_object, MPI, files)."""
     HANDLE_BYTES = 64
 
-    def __init__(self, engine, rank, world, capacity, exchange):
+    def __init__(self, engine, rank, world, capacity, exchange=None):
+        """Creates this rank's gathered array. With `exchange` the handles are swapped and the peers mapped right away; without it the
+        caller passes `self.handle` through its own collective and calls connect(handles) -- the form to use when a rank may fail to
+        create its array: every rank then still takes part in the collective (bench.py does this)."""
         self.eng, self.rank, self.world, self.capacity = engine, rank, world, capacity
         h = _vp()
         buf = C.create_string_buffer(self.HANDLE_BYTES)
         engine._ck(_omo.omo_peer_gather_create(engine.h, rank, world, capacity, C.byref(h), buf), "omo_peer_gather_create")
         self.h = h.value
-        handles = exchange(buf.raw)
-        if len(handles) != world or any(len(x) != self.HANDLE_BYTES for x in handles):
+        self.handle = buf.raw
+        if exchange is not None:
+            self.connect(exchange(self.handle))
+
+    def connect(self, handles):
+        if len(handles) != self.world or any(x is None or len(x) != self.HANDLE_BYTES for x in handles):
             raise EngineError("peer gather: need one 64-byte handle per rank")
-        engine._ck(_omo.omo_peer_gather_connect(self.h, b"".join(handles)), "omo_peer_gather_connect")
+        self.eng._ck(_omo.omo_peer_gather_connect(self.h, b"".join(handles)), "omo_peer_gather_connect")
 
     def eval(self, dX, B_local, first, sync=True):
         """Evaluates this rank's slice [first, first + B_local) of the batch; afterwards values() holds every rank's f."""
