@@ -254,7 +254,7 @@ omo_status omo_multi_eval_grad(omo_multi* m, const double* x, const int* free_id
  * kernel that forms f (finish_kernel's sums, same order, same bits) stores each value straight into EVERY rank's gathered array
  * through cudaIpc-mapped peer memory, its last block publishes "rank r's slice of call k is complete" in every rank's flag
  * array and waits for the other ranks' flags: compute step and exchange are one launch, no NCCL in the data path (8 B200s,
- * one 4096-candidate batch: 0.170 -> 0.161 ms per step against finish_kernel + ncclAllGather, same bits). Calls alternate
+ * one 4096-candidate batch: 0.163 -> 0.156 ms per step against finish_kernel + ncclAllGather, same bits). Calls alternate
  * between two halves of the array, so a rank may still read call k while a faster one delivers k + 1.
  *   1. every rank: omo_peer_gather_create(ctx, rank, world, capacity, &g, handle)      capacity = values of the whole batch
  *   2. exchange the OMO_IPC_HANDLE_BYTES-byte handles between the processes (any transport), in rank order
