@@ -126,6 +126,7 @@ struct omo_ctx {
     std::vector<int> free_uploaded;
     std::vector<double> h_cols;
     double* d_Xfree = nullptr; size_t xfree_cap = 0;   // omo_eval_free: the candidates' free entries as they arrive from the host
+    std::vector<double> xbase_uploaded; bool xbase_is_free_base = false;   // what d_xbase holds, if omo_eval_free put it there (the gradient paths write d_xbase too)
     int* d_inv_free = nullptr; std::vector<int> inv_free_of;   // descriptor index -> position in the free list (-1: frozen), and the free list it was built from
 
     // single-candidate call (the NLopt callback, core_opt.cpp:42-57): H2D of x -> prepare -> objective -> finish -> D2H of f and
@@ -1537,16 +1538,26 @@ omo_status omo_eval_free(omo_ctx* ctx, const double* x_base, const int* free_idx
     if ((st = ensure_capacity(ctx, B)) != OMO_OK) return st;
     if (!ctx->d_xbase) { if ((st = dev_alloc(ctx, &ctx->d_xbase, (size_t)ctx->D)) != OMO_OK) return st; }
     if ((size_t)B * F > ctx->xfree_cap) { if ((st = dev_alloc(ctx, &ctx->d_Xfree, (size_t)B * F)) != OMO_OK) return st; ctx->xfree_cap = (size_t)B * F; }
-    OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x_base, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    // x_base travels only when it changed (a solve expands every batch over the same x_initial, core_opt.cpp:99-121): the upload from
+    // pageable memory and the synchronisation behind it cost ~20 us of a 1.1 ms call
+    bool synced = true;
+    if (ctx->xbase_uploaded.size() != (size_t)ctx->D || ctx->xbase_is_free_base == false ||
+        std::memcmp(ctx->xbase_uploaded.data(), x_base, (size_t)ctx->D * sizeof(double)) != 0) {
+        OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x_base, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        ctx->xbase_uploaded.assign(x_base, x_base + ctx->D);
+        ctx->xbase_is_free_base = true;
+        synced = false;
+    }
     // descriptor index -> position in the free list: the expansion is then one gather per element, parallel over the whole batch
     if (!ctx->d_inv_free || ctx->inv_free_of.size() != (size_t)F || !std::equal(ctx->inv_free_of.begin(), ctx->inv_free_of.end(), free_idx)) {
+        synced = false;
         std::vector<int> inv((size_t)std::max(ctx->D, 1), -1);
         for (int k = 0; k < F; ++k) inv[free_idx[k]] = k;          // a repeated index: the last entry wins, as a serial scatter would
         OMO_CUDA(cudaStreamSynchronize(ctx->stream));
         if ((st = upload(ctx, &ctx->d_inv_free, inv)) != OMO_OK) return st;
         ctx->inv_free_of.assign(free_idx, free_idx + F);
     }
-    OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // x_base and the map came from pageable memory
+    if (!synced) OMO_CUDA(cudaStreamSynchronize(ctx->stream));   // x_base and the map came from pageable memory
     return eval_host_pipelined(ctx, Xfree, B, F, ctx->d_Xfree, true, F, f_out, terms_out);
 }
 
@@ -1737,6 +1748,7 @@ omo_status omo_eval_grad_columns(omo_ctx* ctx, const double* x, const int* free_
             return OMO_OK;
         }
     }
+    ctx->xbase_is_free_base = false;   // d_xbase no longer holds omo_eval_free's base
     OMO_CUDA(cudaMemcpyAsync(ctx->d_xbase, x, (size_t)ctx->D * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     omo::perturb_kernel<<<rows, 128, 0, ctx->stream>>>(ctx->d_xbase, ctx->d_free, ctx->D, h, col_begin, col_count, ctx->d_X);
     OMO_CUDA(cudaGetLastError());
