@@ -147,6 +147,7 @@ struct omo_ctx {
     int self_out_cap = 0;
     int self_spin_slots = 0;                    // outputs of the self-preparing launch in flight that the host polls in h_self_out (0: wait on the stream)
     int self_host_tiles = 0;                    // > 0: single candidate whose tile partials the HOST adds up (slots 4 .. of h_self_out), see launch_self
+    int self_host_rows = 0, self_host_base = -1, self_host_ntiles = 0, self_host_off = 0;   // > 0 rows: a small gradient reduced on the host the same way
     int self_spin_mode = -1;                    // OMO_SPIN=0: always wait on the stream
     unsigned long long self_launches = 0;
 
@@ -1007,7 +1008,8 @@ bool self_usable(omo_ctx* ctx)
     return ctx->self_mode == 1 && jit_mode(ctx) != 0 && !ctx->counting && ctx->n_cp >= 1 && ctx->n_cp <= kSelfMaxCp;
 }
 
-omo_status ensure_self_buffers(omo_ctx* ctx, int rows)
+// rows: rows of the launch; slots: doubles the mapped host buffer must hold (0: rows)
+omo_status ensure_self_buffers(omo_ctx* ctx, int rows, int slots = 0)
 {
     omo_status st;
     if (!ctx->d_self_counter) {
@@ -1019,8 +1021,8 @@ omo_status ensure_self_buffers(omo_ctx* ctx, int rows)
         if ((st = dev_alloc(ctx, &ctx->d_self_dparam, (size_t)cap)) != OMO_OK) return st;
         ctx->self_rows_cap = cap;
     }
-    if (std::max(rows, 4) > ctx->self_out_cap) {
-        const int cap = std::max(rows, 256);
+    if (std::max(std::max(rows, slots), 4) > ctx->self_out_cap) {
+        const int cap = std::max(std::max(rows, slots), 256);
         OMO_CUDA(cudaStreamSynchronize(ctx->stream));
         if (ctx->h_self_out) { cudaFreeHost(ctx->h_self_out); ctx->h_self_out = nullptr; }
         OMO_CUDA(cudaHostAlloc((void**)&ctx->h_self_out, (size_t)cap * sizeof(double), cudaHostAllocMapped));
@@ -1040,6 +1042,51 @@ constexpr unsigned long long kSelfSentinel = 0x7ff8dead5e1fbeefull;
 
 omo_status wait_self(omo_ctx* ctx)
 {
+    if (ctx->self_spin_slots > 0 && ctx->self_host_rows > 0) {
+        // small gradient reduced on the host: wait for every listed (row, tile) pair and every row's D_param, then finish_sparse_kernel's sums
+        const int rows = ctx->self_host_rows, base = ctx->self_host_base, nt = ctx->self_host_ntiles, off = ctx->self_host_off;
+        ctx->self_spin_slots = 0; ctx->self_host_rows = 0;
+        const volatile unsigned long long* out = reinterpret_cast<const volatile unsigned long long*>(ctx->h_self_out);
+        const std::vector<int>& items = ctx->h_items;
+        size_t next = 0;
+        int next_row = 0;
+        auto arrived = [&]() {
+            while (next < items.size() && out[off + 2 * items[next]] != kSelfSentinel && out[off + 2 * items[next] + 1] != kSelfSentinel) ++next;
+            if (next < items.size()) return false;
+            while (next_row < rows - 1 && out[off + 2 * rows * nt + next_row] != kSelfSentinel) ++next_row;   // (the base row's D_param is not used)
+            return next_row == rows - 1;
+        };
+        for (unsigned spin = 1;; ++spin) {
+            if (arrived()) break;
+            if ((spin & 2047u) == 0u) {
+                const cudaError_t q = cudaStreamQuery(ctx->stream);
+                if (q == cudaSuccess) {
+                    if (arrived()) break;
+                    return fail(ctx, OMO_CUDA_ERROR, "self-preparing kernel finished without writing all of its outputs");
+                }
+                if (q != cudaErrorNotReady) { ctx->err = std::string("self-preparing launch: ") + cudaGetErrorString(q); return OMO_CUDA_ERROR; }
+            }
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+        }
+        volatile double* h = ctx->h_self_out;
+        const volatile double* part = h + off;
+        const volatile double* dpar = h + off + 2 * rows * nt;
+        for (int r = 0; r < rows - 1; ++r) {
+            const int l = ctx->h_lo[r], hi = ctx->h_hi[r];
+            double C = 0.0, Dt = 0.0;
+            for (int tl = 0; tl < nt; ++tl) {
+                const int row = (tl >= l && tl <= hi) ? r : base;
+                C = C + part[((size_t)row * nt + tl) * 2];
+                Dt = Dt + part[((size_t)row * nt + tl) * 2 + 1];
+            }
+            double Dp = 0.0;
+            Dp = Dp + dpar[r];
+            h[r] = (C + Dp) + Dt;
+        }
+        return OMO_OK;
+    }
     if (ctx->self_spin_slots > 0) {
         const int n = ctx->self_spin_slots, host_tiles = ctx->self_host_tiles;
         ctx->self_spin_slots = 0; ctx->self_host_tiles = 0;
@@ -1105,7 +1152,7 @@ omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_ro
     // results into the context's mapped host buffer: the host polls the output slots themselves (wait_self) instead of paying the stream
     // synchronisation's round trip through the driver
     if (ctx->self_spin_mode < 0) { const char* e = std::getenv("OMO_SPIN"); ctx->self_spin_mode = (e && std::atoi(e) == 0) ? 0 : 1; }
-    ctx->self_spin_slots = 0; ctx->self_host_tiles = 0;
+    ctx->self_spin_slots = 0; ctx->self_host_tiles = 0; ctx->self_host_rows = 0;
     if (out == ctx->d_self_out && ctx->self_spin_mode == 1 && !ctx->timing) {
         unsigned long long* slots = reinterpret_cast<unsigned long long*>(ctx->h_self_out);
         if (rows == 1 && d_item_map == nullptr && 5 + 2 * plan.n_tiles <= ctx->self_out_cap) {
@@ -1118,6 +1165,19 @@ omo_status launch_self(omo_ctx* ctx, const double* x_host, int rows, int base_ro
             ctx->self_host_tiles = plan.n_tiles;
             for (int i = 4; i < 5 + 2 * plan.n_tiles; ++i) slots[i] = kSelfSentinel;
             ctx->self_spin_slots = 5 + 2 * plan.n_tiles;
+        } else if (rows > 1 && d_item_map != nullptr && base_row == rows - 1 && ctx->sp_valid && (int)ctx->h_lo.size() == rows - 1 &&
+                   ((rows + 3) & ~3) + 2 * rows * plan.n_tiles + rows <= ctx->self_out_cap) {
+            // A small gradient (sparse finite-difference rows + the base row): the listed (row, tile) blocks write their pairs, and each
+            // row's first listed block its D_param, into the mapped buffer behind the result slots; the host applies
+            // finish_sparse_kernel's rule (tiles outside [lo, hi] of a row come from the base row) -- same numbers, same order.
+            const int off = (rows + 3) & ~3;
+            P.partial = ctx->d_self_out + off;
+            P.self_dparam = ctx->d_self_out + off + 2 * rows * plan.n_tiles;
+            P.self_counter = nullptr;
+            for (const int item : ctx->h_items) { slots[off + 2 * item] = kSelfSentinel; slots[off + 2 * item + 1] = kSelfSentinel; }
+            for (int r = 0; r < rows; ++r) slots[off + 2 * rows * plan.n_tiles + r] = kSelfSentinel;
+            ctx->self_host_rows = rows; ctx->self_host_base = base_row; ctx->self_host_ntiles = plan.n_tiles; ctx->self_host_off = off;
+            ctx->self_spin_slots = 1;   // wait_self polls the listed slots itself
         } else {
             const int n_out = rows == 1 ? 4 : (base_row >= 0 ? rows - 1 : rows);   // what self_finish writes: (f, C, D_param, D_traj) or one f per row
             for (int i = 0; i < n_out; ++i) slots[i] = kSelfSentinel;
@@ -1795,7 +1855,8 @@ omo_status omo_eval_grad(omo_ctx* ctx, const double* x, const int* free_idx, int
     if (P + 1 <= kSelfMaxRows && self_usable(ctx)) {
         // the column values are written straight into mapped host memory (by the self-preparing kernel, or by finish_sparse_kernel
         // if that launch is not to be had): no copy-out
-        if ((st = ensure_self_buffers(ctx, P + 1)) != OMO_OK) return st;   // + the base row: launch_self must not move the buffer `out` points into
+        // + the base row, + room for the host-side reduction (launch_self): the buffer `out` points into must not move under the launch
+        if ((st = ensure_self_buffers(ctx, P + 1, ((P + 4) & ~3) + (2 * std::max(ctx->n_tiles, 1) + 1) * (P + 1))) != OMO_OK) return st;
         if ((st = omo_eval_grad_columns(ctx, x, free_idx, F, h, 0, P, ctx->d_self_out, 1)) != OMO_OK) return st;
         std::copy(ctx->h_self_out, ctx->h_self_out + P, ctx->h_cols.begin());
     } else {
