@@ -628,3 +628,30 @@ def test_sorted_curve_work_lists_change_no_bit(monkeypatch, name):
         res[mode] = out
     for a, b in zip(res["0"], res["1"]):
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("name", ["tree24", "stick240"])
+def test_threshold_segment_search_changes_no_bit(monkeypatch, name):
+    """Scenes without sorted work lists find a curve's segment through per-channel thresholds in sample-index space (plan_build /
+    eval_channels_planned: "key time <= t" as "slot >= threshold", a byte-wise SIMD compare); OMO_PLAN=0 keeps the five FP64 compares per
+    curve and sample (eval_channels_staged). Same segment, same record, same value -- with an unsorted chain in the batch, key times
+    outside the window's staged records and w_traj. (stick240 runs its per-sample path here: sorted lists off.)"""
+    scene = synthetic.stick_240(load_scene("stick-figure")) if name == "stick240" else synthetic.tree_scene(n_joints=24, n_frames=400)
+    monkeypatch.setenv("OMO_SORTED_CURVES", "0")
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("OMO_PLAN", mode)
+        c = Core(scene)
+        x0 = c.GetDescriptor()
+        lo, hi = c.window
+        B = 1200 if name == "stick240" else 400
+        X = synthetic.perturbed_candidates(x0, B)
+        X[7, 0] = X[7, 5] + 0.25                       # one candidate's first chain becomes unsorted
+        X[9, 5::5] = X[9, 5::5] + 1e-3                 # another one's key times moved off the sample grid
+        out = [c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True)]
+        c.UpdateGlobalWeight(2.5)
+        out.append(c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True))
+        assert c.engine().jit_info()["launches"] > 0
+        res[mode] = out
+    for a, b in zip(res["0"], res["1"]):
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
