@@ -1228,12 +1228,19 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
     // Large batches travel in chunks on a second stream so that the PCIe copy of chunk i+1 overlaps the kernels of chunk i
     // (the copy of 4096 stick-figure candidates takes about half as long as evaluating them).
     const size_t bytes = (size_t)B * W * sizeof(double);
-    // a chunk is at least 1 MB and at least ~3 waves of objective blocks (chunks alternate between two compute streams, so a chunk's
-    // partial last wave is not lost); at most 4: measured best on stick240 (4: 1.097 ms, 6: 1.108, 8: 1.121). The slices a rank of an
-    // 8-GPU job gets (3.2 MB) still travel in two chunks, so that their copy overlaps their evaluation.
-    const size_t by_work = ((size_t)B * std::max(ctx->n_tiles, 1)) / 2368;
-    int n_chunks = (int)std::max<size_t>(1, std::min<size_t>(4, std::min<size_t>(bytes / ((size_t)1 << 20), by_work)));
+    // Chunk sizes double (1 : 2 : 4 : ...): the kernels cannot start before the first chunk has landed, so it is small, and since a
+    // chunk's copy takes about half as long as its evaluation on this box (PCIe Gen5 against the FP64 pipe), the copy of chunk i+1 (twice
+    // the size) ends when the evaluation of chunk i does -- both engines stay busy. As many chunks (at most 5) as leave the first one
+    // ~1.75 waves of objective blocks and 256 KB: measured on stick240 (4096 candidates, 25.6 MB), e2e per step: ramp 1:2:2:2 1.066 ms,
+    // double x4 1.073, double x5 1.027, double x6 1.075 (its first chunk is less than a wave); free parameters 1.091 -> 1.035.
+    // OMO_EVAL_CHUNKS / OMO_EVAL_CHUNKS_SHAPE=equal | ramp | double override.
+    const long long work_items = (long long)B * std::max(ctx->n_tiles, 1);
+    int n_chunks = 1;
+    while (n_chunks < 5 && work_items / ((1LL << (n_chunks + 1)) - 1) >= 1300 && bytes / (size_t)((1LL << (n_chunks + 1)) - 1) >= ((size_t)256 << 10)) ++n_chunks;
     if (const char* e = std::getenv("OMO_EVAL_CHUNKS")) n_chunks = std::max(1, std::min(8, std::min(B, std::atoi(e))));
+    // every chunk takes the kernel the whole batch would (scene-specialised from 64 K sample-evals up): a small first chunk must not switch
+    // to the table-driven kernel, whose results differ in the last ulps
+    struct HintScope { omo_ctx* c; int saved; HintScope(omo_ctx* c_, int B_) : c(c_), saved(c_->batch_hint) { c->batch_hint = std::max(saved, B_); } ~HintScope() { c->batch_hint = saved; } } hint_scope(ctx, B);
     auto evaluate = [&](int b0, int nb) -> omo_status {
         if (expand) {
             const long long n = (long long)nb * ctx->D;
@@ -1256,12 +1263,10 @@ omo_status eval_host_pipelined(omo_ctx* ctx, const double* X, int B, int W, doub
         // d_X may still be read by kernels queued earlier on `stream`
         OMO_CUDA(cudaEventRecord(ctx->done_ev, ctx->stream));
         OMO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->done_ev, 0));
-        // Chunk sizes 1 : 2 : 2 : ... -- the kernels cannot start before the first chunk has landed, so it is half a chunk; the
-        // rest are equal because on this box the copy (~25 GB/s) takes about as long as the evaluation, and the step then ends
-        // one chunk's evaluation after the last copy. OMO_EVAL_CHUNKS_SHAPE=equal | ramp (default) | double (1 : 2 : 4 : ...).
+        // OMO_EVAL_CHUNKS_SHAPE=equal | ramp (1 : 2 : 2 : ...) | double (default, 1 : 2 : 4 : ...)
         int bound[9];
         const char* shape = std::getenv("OMO_EVAL_CHUNKS_SHAPE");
-        const int mode_c = !shape ? 1 : (std::strcmp(shape, "equal") == 0 ? 0 : (std::strcmp(shape, "double") == 0 ? 2 : 1));
+        const int mode_c = !shape ? 2 : (std::strcmp(shape, "equal") == 0 ? 0 : (std::strcmp(shape, "ramp") == 0 ? 1 : 2));
         for (int c = 0; c <= n_chunks; ++c) {
             long long num = c, den = n_chunks;
             if (mode_c == 1) { num = c == 0 ? 0 : 2 * c - 1; den = 2 * n_chunks - 1; }
