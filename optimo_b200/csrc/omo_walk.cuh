@@ -774,6 +774,70 @@ struct Walker {
         }
     }
 
+    // The per-sample form of a curve group with K curves in lockstep per thread instead of three (the generator's choice per scene,
+    // omo_jit.hpp curve_k: more independent Newton chains per warp where only 12 warps fit an SM). Same curves, same arithmetic per
+    // curve: which curves share a lockstep round changes no bit.
+    template <int K>
+    __device__ __forceinline__ void curve_staged_n(const int buf, const int i0, const int lc0)
+    {
+        const OmoDevScene& S = c_scene;
+        int ch[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) ch[k] = S.grp_list[i0 + k];
+        double val[K];
+        if (!sorted) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                unsigned eb = 0, en = 0;
+                val[k] = COUNT ? eval_channel<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false, eb, en)
+                               : eval_channel_slow<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], S.chan_n[ch[k]], t, false);
+                if (COUNT && owned) { n_bez += eb; n_newton += en; }
+            }
+        } else {
+            const double* sk[K];
+            int nn[K], base[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                sk[k] = SELF ? seg_sm + (size_t)(S.chan_pos[ch[k]] + wbase[i0 + k]) * OMO_SEGD
+                             : wsb + (size_t)((buf * SEGG + lc0 + k) * OMO_SEGW) * OMO_SEGD;
+                nn[k] = S.chan_n[ch[k]];
+                base[k] = wbase[i0 + k];
+            }
+            unsigned fb = 0, eb = 0, en = 0;
+            double tk[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) tk[k] = t;
+            if constexpr (OMO_PLAN != 0 && !SELF) {
+                unsigned long long plan[K];
+                int sik[K];
+                const unsigned long long* __restrict__ wp = wplan + (tid >> 5) * SEGG + lc0;
+#pragma unroll
+                for (int k = 0; k < K; ++k) { plan[k] = wp[k]; sik[k] = idx; }
+                eval_channels_planned<K, COUNT>(sk, plan, sik, tk, val, fb, eb, en);
+            } else
+            eval_channels_staged<K, COUNT>(sk, nn, base, tk, val, fb, eb, en);
+            if (fb) {
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (fb >> k & 1u)
+                        val[k] = COUNT ? eval_channel<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true, eb, en)
+                                       : eval_channel_slow<!SELF>(pc, P.n_cp, S.chan_pos[ch[k]], nn[k], t, true);
+            }
+            if (COUNT && owned) { n_bez += eb; n_newton += en; }
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) ex[S.chan_row[ch[k]] * NT + idx] = val[k];
+    }
+
+    template <int K, int REM>
+    __device__ __forceinline__ void curve_group_n(const int buf, const int g0, const int nk)
+    {
+        if (OMO_PLAN != 0 && SEGG > 0 && !SELF && sorted) plan_build(buf, g0, K * nk + REM);
+#pragma unroll 1
+        for (int c = 0; c < nk; ++c) curve_staged_n<K>(buf, g0 + K * c, K * c);
+        if (REM > 0) curve_staged_n<(REM > 0 ? REM : 1)>(buf, g0 + K * nk, K * nk);
+    }
+
     // ---- the same steps with the scene's structural zeros resolved at compile time (scene-specialised kernels) ---------
     // Channel kind Kk of the body's angle k: 0 = keyed (exchange row, stencil, sincos), 1 = constant (sin / cos / stencil
     // residue from the scene table), 3 = the constant 0 (sin = ZeroT, cos = OneT, qd = qdd = ZeroT). ZB: omo_rnea_z.cuh.
