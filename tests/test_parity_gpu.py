@@ -655,3 +655,31 @@ def test_threshold_segment_search_changes_no_bit(monkeypatch, name):
         res[mode] = out
     for a, b in zip(res["0"], res["1"]):
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_curve_group_forms_change_no_bit(monkeypatch):
+    """A scene that takes no sorted work lists gets its curve groups as curve_group_n<K, REM> (omo_jit.hpp curve_k): the per-sample
+    triples without the sorted form compiled beside them. OMO_CURVE_K=0 restores curve_group<REM>, OMO_CURVE_K=4 solves four curves per
+    lockstep round (remainder groups included): which curves share a round changes nothing in a curve's own arithmetic. With an
+    unsorted chain, key times off the sample grid and w_traj, as above."""
+    scene = synthetic.tree_scene(n_joints=24, n_frames=400)
+    res = {}
+    for mode in ("0", None, "4"):
+        if mode is None:
+            monkeypatch.delenv("OMO_CURVE_K", raising=False)
+        else:
+            monkeypatch.setenv("OMO_CURVE_K", mode)
+        c = Core(scene)
+        x0 = c.GetDescriptor()
+        lo, hi = c.window
+        X = synthetic.perturbed_candidates(x0, 400)
+        X[7, 0] = X[7, 5] + 0.25
+        X[9, 5::5] = X[9, 5::5] + 1e-3
+        out = [c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True)]
+        c.UpdateGlobalWeight(2.5)
+        out.append(c.CalculateFullObjectiveBatch(lo, hi, X, x0, want_terms=True))
+        assert c.engine().jit_info()["launches"] > 0
+        res[mode] = out
+    for mode in (None, "4"):
+        for a, b in zip(res["0"], res[mode]):
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
