@@ -77,5 +77,23 @@ __device__ __forceinline__ void sincos_angle(const double x, double* __restrict_
     *c_out = co;
 }
 
+// Out-of-line forms (one copy of the code per kernel instead of one per keyed angle; OMO_SINCOS_CALL in omo_walk.cuh): the same
+// operations on the same operands -- same bits as the inline form. Six doubles come back in registers.
+struct SinCos3 { double s0, c0, s1, c1, s2, c2; };
+__device__ __noinline__ SinCos3 sincos_angle3(const double x0, const double x1, const double x2)
+{
+    SinCos3 r;
+    sincos_angle(x0, &r.s0, &r.c0);
+    sincos_angle(x1, &r.s1, &r.c1);
+    sincos_angle(x2, &r.s2, &r.c2);
+    return r;
+}
+__device__ __noinline__ double2 sincos_angle1(const double x)
+{
+    double2 r;
+    sincos_angle(x, &r.x, &r.y);
+    return r;
+}
+
 }  // namespace omo
 #endif

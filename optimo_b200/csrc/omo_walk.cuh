@@ -30,6 +30,9 @@
 #ifndef OMO_PLAN
 #define OMO_PLAN 0
 #endif
+#ifndef OMO_SINCOS_CALL
+#define OMO_SINCOS_CALL 0   // 1: a body with three keyed angles calls sincos_angle3 (out of line); 2: every keyed angle calls sincos_angle1
+#endif
 #define OMO_PLAN_PAD 16   // plan area rounded up to 16 words = 128 bytes (omo_jit.hpp: place_slots reserves the same)
 
 namespace omo {
@@ -857,6 +860,7 @@ struct Walker {
         constexpr int kind[3] = {K0, K1, K2};
         const int rowk[3] = {row0, row1, row2};
         double qd[3] = {0.0, 0.0, 0.0}, qdd[3] = {0.0, 0.0, 0.0}, ss[3] = {0.0, 0.0, 0.0}, cc[3] = {1.0, 1.0, 1.0};
+        [[maybe_unused]] double xq[3] = {0.0, 0.0, 0.0};
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             if (kind[k] == 0) {
@@ -876,12 +880,18 @@ struct Walker {
                     qd[k] = (p1 - m1) * P.inv_2dt;
                     qdd[k] = (p1 - 2.0 * x + m1) * P.inv_dt2;
                 }
-                sincos_angle(x, &ss[k], &cc[k]);
+                if constexpr (OMO_SINCOS_CALL == 1 && K0 == 0 && K1 == 0 && K2 == 0) xq[k] = x;
+                else if constexpr (OMO_SINCOS_CALL == 2) { const double2 r = sincos_angle1(x); ss[k] = r.x; cc[k] = r.y; }
+                else sincos_angle(x, &ss[k], &cc[k]);
             } else if (kind[k] == 1) {
                 ss[k] = S.chan_sin[3 * b + k]; cc[k] = S.chan_cos[3 * b + k];
                 qd[k] = interior ? S.chan_qd[3 * b + k] : 0.0;
                 qdd[k] = interior ? S.chan_qdd[3 * b + k] : 0.0;
             }
+        }
+        if constexpr (OMO_SINCOS_CALL == 1 && K0 == 0 && K1 == 0 && K2 == 0) {
+            const SinCos3 r = sincos_angle3(xq[0], xq[1], xq[2]);
+            ss[0] = r.s0; cc[0] = r.c0; ss[1] = r.s1; cc[1] = r.c1; ss[2] = r.s2; cc[2] = r.c2;
         }
         s0 = ss[0]; s1 = ss[1]; s2 = ss[2]; c0 = cc[0]; c1 = cc[1]; c2 = cc[2];
         const auto sc = make_sc<K0, K1, K2>(ss[0], cc[0], ss[1], cc[1], ss[2], cc[2]);
