@@ -184,3 +184,38 @@ def test_write_json_is_byte_for_byte_what_json11_writes(name):
         text = c.scene_json()
         canon = subprocess.run([helper, "canon"], input=text.encode(), capture_output=True, check=True).stdout.decode()
         assert text == canon
+
+
+def test_generator_chooses_the_curve_group_form_per_scene(tmp_path, monkeypatch):
+    """omo_jit.hpp on the host (NVRTC needs no GPU): a scene on sorted curve work lists keeps curve_group<REM> (both forms, chosen at
+    launch time), a many-group scene gets curve_group_n<3, REM> (the per-sample form alone); OMO_CURVE_K / OMO_SINCOS_CALL select the
+    measured-and-not-kept forms, which still compile."""
+    import re
+
+    for k in ("OMO_CURVE_K", "OMO_SINCOS_CALL", "OMO_SORTED_CURVES", "OMO_PLAN", "OMO_JIT_DEFINES"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("OMO_JIT_CACHE", "0")   # compile, do not read or write the in-tree cubin cache
+
+    def forms(scene, tag, **kw):
+        prefix = str(tmp_path / tag)
+        ok, log = Core(scene).probe_specialised_kernel(dump_prefix=prefix, **kw)
+        if not ok and "NVRTC unavailable" in log:
+            pytest.skip("no libnvrtc on this machine")
+        assert ok, log[:2000]
+        src = open(prefix + ".cu").read()
+        return set(re.findall(r"w\.(curve_group(?:_n)?<[^>]*>)", src)), src
+
+    stick, src = forms(load_scene("stick-figure"), "stick")
+    assert stick and all(f.startswith("curve_group<") for f in stick)
+    assert "#define OMO_PLAN 0" in src and "#define OMO_SINCOS_CALL 0" in src
+    tree = synthetic.tree_scene(n_joints=24, n_frames=120)
+    t3, src = forms(tree, "tree")
+    assert t3 and all(f.startswith("curve_group_n<3,") for f in t3)
+    assert "#define OMO_PLAN 1" in src
+    monkeypatch.setenv("OMO_CURVE_K", "4")
+    monkeypatch.setenv("OMO_SINCOS_CALL", "1")
+    t4, src = forms(tree, "tree4")
+    assert t4 and all(f.startswith("curve_group_n<4,") for f in t4) and "#define OMO_SINCOS_CALL 1" in src
+    monkeypatch.setenv("OMO_CURVE_K", "0")
+    t0, _ = forms(tree, "tree0")
+    assert t0 and all(f.startswith("curve_group<") for f in t0)
